@@ -1,0 +1,188 @@
+/*
+ * msk144_b200.h -- C ABI of libmsk144b200.so, the B200-native MSK144 stream decoder.
+ *
+ * Drop-in boundary for the hot path of alexander-sholohov/msk144cudecoder ("the reference"):
+ *   sample block -> analytic signal -> sync search -> soft bits -> LDPC(128,90) -> 77-bit payload -> text.
+ * The reference has no library boundary of its own: its de-facto operator API is
+ *   MSK144SearchContext ctx(center, width, step, depth, thr)          (msk_context.cuh:23)
+ *   do_decode(ctx, device_block5184, ResultFilter&, SNRTracker&)      (main.cu:53,428-532)
+ *   ResultKeeper::get_all_results() -> ResultItem[]                   (result_keeper.cuh:123)
+ * inside the process loop of main.cu:261-425.  Every entry point below names the piece it replaces.
+ *
+ * Conventions: plain C, no exceptions cross the boundary; every function returns 0 on success or a
+ * negative MSK144_E* code, and msk144_last_error() gives the text for the calling thread.  One
+ * decoder owns one GPU and its streams; a decoder is used from one thread at a time.  There is NO
+ * CPU fallback: creation fails if no sm_100-class device is usable.
+ */
+#ifndef MSK144_B200_H
+#define MSK144_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MSK144_BLOCK_SAMPLES 5184 /* common.h:15  Num6x864 */
+#define MSK144_HOP_SAMPLES 2592   /* main.cu:284-288 */
+#define MSK144_NLLR 128           /* common.h:26 */
+#define MSK144_NMSG 77            /* common.h:27 */
+#define MSK144_NCAND 8            /* common.h:34 */
+
+enum {
+    MSK144_OK = 0,
+    MSK144_EINVAL = -1,  /* bad argument / configuration */
+    MSK144_ECUDA = -2,   /* CUDA runtime error (the reference throws std::runtime_error) */
+    MSK144_ENODEV = -3,  /* no usable GPU */
+    MSK144_ENOMEM = -4,
+    MSK144_EOVERFLOW = -5 /* an output array was too small; counts are still returned */
+};
+
+/* flags */
+enum {
+    /* Reproduce the reference's decode_cache comparator quirk (main.cu:430-447): within one block every
+     * candidate after the first decoded one is reported with the FIRST candidate's text.  The CLI sets
+     * it (output identical to the reference); clear it for per-payload text. */
+    MSK144_FLAG_COMPAT_DECODE_CACHE = 1
+};
+
+/* The seven CLI values of main.cu:124-133 + placement.  Zero-initialise, then msk144_config_defaults(). */
+typedef struct msk144_config {
+    float center_frequency_hz; /* --center-frequency; 1500 audio / 0 IQ (main.cu:193-208) */
+    float search_step_hz;      /* --search-step, 2.0 */
+    float search_width_hz;     /* --search-width, 200.0 */
+    int32_t scan_depth;        /* --scan-depth, 4; clamped to [1,8] (msk_context.cuh:28-33) */
+    int32_t read_mode;         /* --read-mode: 1 = s16 mono audio, 2 = s8 I/Q pairs (main.cu:79-83) */
+    int32_t analytic_method;   /* --analytic-method: 1 = FFT, 2 = shift/LPF/shift (audio only) */
+    int32_t nbadsync_threshold; /* --nbadsync-threshold, 1 */
+    int32_t device;            /* CUDA device ordinal */
+    int32_t max_batch_blocks;  /* blocks per launch group (0 = default 256) */
+    int32_t flags;             /* MSK144_FLAG_* */
+    int32_t reserved[6];
+} msk144_config;
+
+/* One printed decode line == ResultFilter::ResultItem (result_filter.h:17-29) + provenance. */
+typedef struct msk144_line {
+    int64_t block_index; /* block number within its channel, hop = 2592 samples */
+    int32_t channel;
+    int32_t snr;
+    float f0;
+    int32_t num_avg;
+    int32_t nbadsync;
+    int32_t pattern_idx;
+    uint8_t payload[80]; /* 77 bits (0/1) of the candidate this line was printed for */
+    char text[40];       /* NUL terminated, right-trimmed (decode_softbits.cpp:50-53) */
+} msk144_line;
+
+/* One LDPC success == the fields of ResultKeeper::ResultItem (result_keeper.cuh:16-30) that leave
+ * the GPU.  item_index = (freq_idx * depth + pattern_idx) * 8 + slot (result_keeper.cuh:85-91). */
+typedef struct msk144_result {
+    int64_t block_index;
+    int32_t channel;
+    uint32_t item_index;
+    uint32_t freq_idx;
+    uint32_t pattern_idx;
+    uint32_t slot;
+    uint32_t pos;
+    float f0;
+    float xb;
+    int32_t num_avg;
+    int32_t nbadsync;
+    int32_t ldpc_iters;
+    int32_t ldpc_nhard;
+    uint8_t message[80]; /* 77 bits, 0/1 */
+} msk144_result;
+
+/* One scan candidate (every (frequency, pattern, slot), decoded or not). */
+typedef struct msk144_candidate {
+    uint32_t pos;     /* 0..5375, as the reference reports it (scan_kernel.cuh:358-364) */
+    float xb;
+    int32_t nbadsync;
+    int32_t llr_slot; /* index into the LLR queue if nbadsync <= threshold, else -1 */
+} msk144_candidate;
+
+typedef struct msk144_info {
+    int32_t num_freqs;       /* NF, msk_context.cuh:102-108 */
+    int32_t scan_depth;      /* effective depth */
+    int32_t items_per_block; /* NF * depth * 8 */
+    int32_t sm_count;
+    float left_hz, right_hz; /* msk_context.cuh:127-129 */
+    int32_t max_batch_blocks;
+    int32_t reserved[9];
+} msk144_info;
+
+/* Timing of the last completed launch group, CUDA events on the decoder's stream (milliseconds). */
+typedef struct msk144_stage_times {
+    float frontend_ms, scan_ms, ldpc_ms, total_ms;
+    int64_t blocks;        /* blocks in the group */
+    int64_t llr_codewords; /* candidates that passed the nbadsync gate */
+    int64_t ldpc_successes;
+    int64_t kernel_launches; /* kernels launched by this library since creation */
+} msk144_stage_times;
+
+typedef struct msk144_decoder msk144_decoder;
+
+const char* msk144_last_error(void);
+void msk144_config_defaults(msk144_config* cfg); /* code defaults of main.cu:124-133 */
+
+/* MSK144SearchContext ctor + Analytic ctor + LDPCContext::init (main.cu:224-226). */
+int msk144_create(const msk144_config* cfg, msk144_decoder** out);
+void msk144_destroy(msk144_decoder* dec);
+int msk144_get_info(const msk144_decoder* dec, msk144_info* info);
+int msk144_get_stage_times(const msk144_decoder* dec, msk144_stage_times* t);
+
+/* ---- streaming surface: the while(true) loop of main.cu:261-425 ------------------------------------
+ * push raw stdin bytes (s16le mono, or s8 I,Q pairs); the library owns the half-block overlap, runs
+ * every complete block, keeps the SNR recurrence, and queues decode lines in output order. */
+int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes);
+int msk144_poll(msk144_decoder* dec, msk144_line* lines, size_t cap, size_t* nlines);
+int msk144_reset_stream(msk144_decoder* dec);
+
+/* ---- batch surface: nchan independent channels, each samples_per_channel samples, back to back.
+ * Blocks of a channel start every 2592 samples; channels with fewer than 5184 samples yield nothing.
+ * Each channel starts a fresh SNR recurrence.  lines / results may be NULL (cap 0).
+ * `_host`: samples in host memory (pinned or pageable) -- H2D and D2H are inside the call.
+ * `_device`: samples already resident in device memory; `stream` is a cudaStream_t (NULL = the
+ * decoder's own stream).  Both return after the results are on the host. */
+int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t samples_per_channel, int nchan,
+                       msk144_line* lines, size_t line_cap, size_t* nlines,
+                       msk144_result* results, size_t result_cap, size_t* nresults);
+int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t samples_per_channel, int nchan,
+                         void* stream, msk144_line* lines, size_t line_cap, size_t* nlines,
+                         msk144_result* results, size_t result_cap, size_t* nresults);
+
+/* Device-only pass for measurement: runs the kernels on `stream` over resident input and leaves the
+ * results on the device; no host synchronisation, no D2H.  *nblocks_out = blocks processed. */
+int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t samples_per_channel, int nchan,
+                      void* stream, int64_t* nblocks_out);
+
+/* ---- stage-level entry points (tests, micro-benchmarks) ---------------------------------------------- */
+/* main.cu:300-332,365-377 + analytic2.cuh / analytic_fft.cu: raw samples of `nblocks` consecutive
+ * blocks of ONE channel -> filtered complex blocks [nblocks][5184][2] and SNR sub-block powers
+ * [nblocks][8] (snr_tracker.cu:23-32). */
+int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsamples, float* blocks_re_im,
+                         float* powers8, int64_t* nblocks_out);
+/* scan_kernel + softbits_kernel + index_kernel on already filtered blocks (host, [nblocks][5184][2]).
+ * cands: [nblocks][items_per_block]; llr: [llr_cap][128] compacted in arbitrary order, llr_item[i] =
+ * block * items_per_block + item_index of row i. */
+int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nblocks, msk144_candidate* cands,
+                     float* llr, uint32_t* llr_item, size_t llr_cap, size_t* nllr);
+/* ldpc_kernel on caller-supplied LLRs [ncw][128] (BASELINE config 4). found/iters/nhard: [ncw];
+ * msg77: [ncw][77] of 0/1. */
+int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, uint8_t* found, uint8_t* msg77,
+                            int32_t* iters, int32_t* nhard);
+/* Same on device-resident LLRs, asynchronous on `stream`; d_out: [ncw] x 4 uint32 words
+ * {bits 0..31, 32..63, 64..76 | found<<31, iters | nhard<<8}. */
+int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t ncw, uint32_t* d_out, void* stream);
+
+/* ---- host post-processing, exported for the CLI and for callers that bring their own GPU stage ---- */
+/* decode_softbits.cpp:23-55 (i3/n3 gate + unpack77 + right trim). 1 = found. text: >= 38 bytes. */
+int msk144_decode_message(const uint8_t* msg77, char* text);
+/* main.cu:406-419 line format; date14 = "%Y%m%d%H%M%S" local time, NULL = now. Returns length. */
+int msk144_format_line(const msk144_line* line, const char* date14, char* out, size_t cap);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSK144_B200_H */

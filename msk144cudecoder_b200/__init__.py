@@ -1,0 +1,301 @@
+"""msk144cudecoder_b200 -- B200-native MSK144 stream decoder (Python face of libmsk144b200.so).
+
+The product is the C-ABI shared library built from csrc/ (include/msk144_b200.h); this package is a
+thin ctypes binding plus a host-side mirror of the reference's operator interface:
+
+    MSK144SearchContext(center, width, step, depth, nbadsync_threshold)   # msk_context.cuh:23
+    do_decode(ctx, samples) -> decode lines                                # main.cu:428-532
+
+There is no CPU path: if the library is missing, or no sm_100-class GPU is usable, calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+import subprocess
+from typing import List, Optional, Tuple
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libmsk144b200.so")
+CLI_PATH = os.path.join(_HERE, "bin", "msk144cudecoder")
+
+BLOCK_SAMPLES, HOP_SAMPLES = 5184, 2592
+FLAG_COMPAT_DECODE_CACHE = 1
+
+EXPORTED_SYMBOLS = [
+    "msk144_last_error", "msk144_config_defaults", "msk144_create", "msk144_destroy", "msk144_get_info",
+    "msk144_get_stage_times", "msk144_push", "msk144_poll", "msk144_reset_stream", "msk144_decode_host",
+    "msk144_decode_device", "msk144_run_device", "msk144_frontend_host", "msk144_scan_host",
+    "msk144_ldpc_decode_host", "msk144_ldpc_decode_device", "msk144_decode_message", "msk144_format_line",
+]
+
+
+class Msk144Error(RuntimeError):
+    pass
+
+
+class Config(C.Structure):
+    _fields_ = [("center_frequency_hz", C.c_float), ("search_step_hz", C.c_float), ("search_width_hz", C.c_float),
+                ("scan_depth", C.c_int32), ("read_mode", C.c_int32), ("analytic_method", C.c_int32),
+                ("nbadsync_threshold", C.c_int32), ("device", C.c_int32), ("max_batch_blocks", C.c_int32),
+                ("flags", C.c_int32), ("reserved", C.c_int32 * 6)]
+
+
+class Line(C.Structure):
+    _fields_ = [("block_index", C.c_int64), ("channel", C.c_int32), ("snr", C.c_int32), ("f0", C.c_float),
+                ("num_avg", C.c_int32), ("nbadsync", C.c_int32), ("pattern_idx", C.c_int32),
+                ("payload", C.c_uint8 * 80), ("text", C.c_char * 40)]
+
+
+class Info(C.Structure):
+    _fields_ = [("num_freqs", C.c_int32), ("scan_depth", C.c_int32), ("items_per_block", C.c_int32),
+                ("sm_count", C.c_int32), ("left_hz", C.c_float), ("right_hz", C.c_float),
+                ("max_batch_blocks", C.c_int32), ("reserved", C.c_int32 * 9)]
+
+
+class StageTimes(C.Structure):
+    _fields_ = [("frontend_ms", C.c_float), ("scan_ms", C.c_float), ("ldpc_ms", C.c_float), ("total_ms", C.c_float),
+                ("blocks", C.c_int64), ("llr_codewords", C.c_int64), ("ldpc_successes", C.c_int64),
+                ("kernel_launches", C.c_int64)]
+
+
+RESULT_DTYPE = np.dtype([("block_index", "<i8"), ("channel", "<i4"), ("item_index", "<u4"), ("freq_idx", "<u4"),
+                         ("pattern_idx", "<u4"), ("slot", "<u4"), ("pos", "<u4"), ("f0", "<f4"), ("xb", "<f4"),
+                         ("num_avg", "<i4"), ("nbadsync", "<i4"), ("ldpc_iters", "<i4"), ("ldpc_nhard", "<i4"),
+                         ("message", "u1", (80,))], align=True)
+CAND_DTYPE = np.dtype([("pos", "<u4"), ("xb", "<f4"), ("nbadsync", "<i4"), ("llr_slot", "<i4")])
+assert RESULT_DTYPE.itemsize == 136, RESULT_DTYPE.itemsize
+
+_lib = None
+
+
+def build(verbose: bool = False) -> str:
+    """Compile the CUDA library and the CLI in-tree (nvcc -gencode arch=compute_100a,code=sm_100a)."""
+    r = subprocess.run(["make", "-C", os.path.join(_HERE, "csrc")], capture_output=not verbose, text=True)
+    if r.returncode != 0:
+        raise Msk144Error("build failed:\n" + (r.stdout or "") + (r.stderr or ""))
+    return LIB_PATH
+
+
+def lib():
+    """Load libmsk144b200.so.  Fails loudly when it has not been built: there is no fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise Msk144Error(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(the decoder has no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        vp, sz = C.c_void_p, C.c_size_t
+        L.msk144_last_error.restype = C.c_char_p
+        L.msk144_config_defaults.argtypes = [C.POINTER(Config)]
+        L.msk144_create.argtypes = [C.POINTER(Config), C.POINTER(vp)]
+        L.msk144_destroy.argtypes = [vp]
+        L.msk144_destroy.restype = None
+        L.msk144_get_info.argtypes = [vp, C.POINTER(Info)]
+        L.msk144_get_stage_times.argtypes = [vp, C.POINTER(StageTimes)]
+        L.msk144_push.argtypes = [vp, vp, sz]
+        L.msk144_poll.argtypes = [vp, C.POINTER(Line), sz, C.POINTER(sz)]
+        L.msk144_reset_stream.argtypes = [vp]
+        L.msk144_decode_host.argtypes = [vp, vp, sz, C.c_int, C.POINTER(Line), sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        L.msk144_decode_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(Line), sz, C.POINTER(sz), vp, sz,
+                                           C.POINTER(sz)]
+        L.msk144_run_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(C.c_int64)]
+        L.msk144_frontend_host.argtypes = [vp, vp, sz, vp, vp, C.POINTER(C.c_int64)]
+        L.msk144_scan_host.argtypes = [vp, vp, C.c_int64, vp, vp, vp, sz, C.POINTER(sz)]
+        L.msk144_ldpc_decode_host.argtypes = [vp, vp, sz, vp, vp, vp, vp]
+        L.msk144_ldpc_decode_device.argtypes = [vp, vp, sz, vp, vp]
+        L.msk144_decode_message.argtypes = [vp, C.c_char_p]
+        L.msk144_format_line.argtypes = [C.POINTER(Line), C.c_char_p, C.c_char_p, sz]
+        L.msk144_unpack77_reset.argtypes = []
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise Msk144Error(f"msk144 error {rc}: {lib().msk144_last_error().decode('utf-8', 'replace')}")
+
+
+def _line_dict(l: Line) -> dict:
+    return dict(block=int(l.block_index), channel=int(l.channel), snr=int(l.snr), f0=float(l.f0),
+                num_avg=int(l.num_avg), nbadsync=int(l.nbadsync), pattern_idx=int(l.pattern_idx),
+                payload=bytes(bytearray(l.payload)[:77]), text=l.text.decode("ascii", "replace"))
+
+
+class Decoder:
+    """One GPU decoder instance (msk144_create .. msk144_destroy)."""
+
+    def __init__(self, center: Optional[float] = None, width: float = 200.0, step: float = 2.0, depth: int = 4,
+                 thr: int = 1, read_mode: int = 1, method: int = 2, device: int = 0, max_batch_blocks: int = 128,
+                 compat_cache: bool = True):
+        L = lib()
+        cfg = Config()
+        L.msk144_config_defaults(C.byref(cfg))
+        cfg.center_frequency_hz = (1500.0 if read_mode == 1 else 0.0) if center is None else center
+        cfg.search_width_hz, cfg.search_step_hz, cfg.scan_depth = width, step, depth
+        cfg.nbadsync_threshold, cfg.read_mode, cfg.analytic_method = thr, read_mode, method
+        cfg.device, cfg.max_batch_blocks = device, max_batch_blocks
+        cfg.flags = FLAG_COMPAT_DECODE_CACHE if compat_cache else 0
+        self.cfg = cfg
+        self._h = C.c_void_p()
+        _check(L.msk144_create(C.byref(cfg), C.byref(self._h)))
+        info = Info()
+        _check(L.msk144_get_info(self._h, C.byref(info)))
+        self.num_freqs, self.depth, self.items_per_block = info.num_freqs, info.scan_depth, info.items_per_block
+        self.sm_count = info.sm_count
+        self.left_hz, self.right_hz = info.left_hz, info.right_hz
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().msk144_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # -- batch ---------------------------------------------------------------------------------
+    def _decode(self, fn, ptr, spc, nchan, extra, line_cap, result_cap):
+        lines = (Line * line_cap)()
+        results = np.zeros(result_cap, RESULT_DTYPE)
+        nl, nr = C.c_size_t(0), C.c_size_t(0)
+        rc = fn(self._h, ptr, spc, nchan, *extra, lines, line_cap, C.byref(nl), results.ctypes.data, result_cap,
+                C.byref(nr))
+        if rc == -5 and (nl.value > line_cap or nr.value > result_cap):  # grow and retry once
+            return self._decode(fn, ptr, spc, nchan, extra, max(line_cap, nl.value), max(result_cap, nr.value))
+        _check(rc)
+        return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
+
+    def decode_host(self, samples: np.ndarray, nchan: int = 1, line_cap: int = 4096, result_cap: int = 1 << 16):
+        """samples: int16 (audio) or int8 I,Q pairs, `nchan` equal-length channels back to back."""
+        samples = np.ascontiguousarray(samples)
+        spc = samples.nbytes // 2 // nchan
+        return self._decode(lib().msk144_decode_host, samples.ctypes.data, spc, nchan, (), line_cap, result_cap)
+
+    def decode_device(self, dev_ptr: int, samples_per_channel: int, nchan: int = 1, stream: int = 0,
+                      line_cap: int = 4096, result_cap: int = 1 << 16):
+        return self._decode(lib().msk144_decode_device, dev_ptr, samples_per_channel, nchan, (C.c_void_p(stream),),
+                            line_cap, result_cap)
+
+    def run_device(self, dev_ptr: int, samples_per_channel: int, nchan: int = 1, stream: int = 0) -> int:
+        nb = C.c_int64(0)
+        _check(lib().msk144_run_device(self._h, dev_ptr, samples_per_channel, nchan, C.c_void_p(stream), C.byref(nb)))
+        return int(nb.value)
+
+    def stage_times(self) -> dict:
+        t = StageTimes()
+        _check(lib().msk144_get_stage_times(self._h, C.byref(t)))
+        return {k: getattr(t, k) for k, _ in StageTimes._fields_}
+
+    # -- streaming -------------------------------------------------------------------------------
+    def push(self, data: bytes):
+        _check(lib().msk144_push(self._h, data, len(data)))
+
+    def poll(self, cap: int = 1024) -> List[dict]:
+        lines = (Line * cap)()
+        n = C.c_size_t(0)
+        _check(lib().msk144_poll(self._h, lines, cap, C.byref(n)))
+        return [_line_dict(lines[i]) for i in range(n.value)]
+
+    def reset_stream(self):
+        _check(lib().msk144_reset_stream(self._h))
+
+    # -- stages ----------------------------------------------------------------------------------
+    def frontend(self, samples: np.ndarray) -> Tuple[np.ndarray, np.ndarray]:
+        samples = np.ascontiguousarray(samples)
+        ns = samples.nbytes // 2
+        nb = (ns - BLOCK_SAMPLES) // HOP_SAMPLES + 1 if ns >= BLOCK_SAMPLES else 0
+        blocks = np.zeros((nb, BLOCK_SAMPLES), np.complex64)
+        powers = np.zeros((nb, 8), np.float32)
+        n = C.c_int64(0)
+        _check(lib().msk144_frontend_host(self._h, samples.ctypes.data, ns, blocks.ctypes.data, powers.ctypes.data,
+                                          C.byref(n)))
+        return blocks, powers
+
+    def scan(self, blocks: np.ndarray):
+        """blocks: complex64 [nblocks, 5184].  Returns (cands[nblocks, items], llr[n,128], llr_item[n])."""
+        blocks = np.ascontiguousarray(blocks, np.complex64).reshape(-1, BLOCK_SAMPLES)
+        nb = blocks.shape[0]
+        cands = np.zeros((nb, self.items_per_block), CAND_DTYPE)
+        cap = nb * self.items_per_block
+        llr = np.zeros((cap, 128), np.float32)
+        item = np.zeros(cap, np.uint32)
+        n = C.c_size_t(0)
+        _check(lib().msk144_scan_host(self._h, blocks.ctypes.data, nb, cands.ctypes.data, llr.ctypes.data,
+                                      item.ctypes.data, cap, C.byref(n)))
+        return cands, llr[:n.value].copy(), item[:n.value].copy()
+
+    def ldpc_decode(self, llr: np.ndarray):
+        llr = np.ascontiguousarray(llr, np.float32).reshape(-1, 128)
+        n = llr.shape[0]
+        found = np.zeros(n, np.uint8)
+        msg = np.zeros((n, 77), np.uint8)
+        iters = np.zeros(n, np.int32)
+        nhard = np.zeros(n, np.int32)
+        _check(lib().msk144_ldpc_decode_host(self._h, llr.ctypes.data, n, found.ctypes.data, msg.ctypes.data,
+                                             iters.ctypes.data, nhard.ctypes.data))
+        return found.astype(bool), msg, iters, nhard
+
+    def ldpc_decode_device(self, d_llr: int, ncw: int, d_out: int, stream: int = 0):
+        _check(lib().msk144_ldpc_decode_device(self._h, d_llr, ncw, d_out, C.c_void_p(stream)))
+
+
+# ---- mirror of the reference's operator interface ---------------------------------------------------
+class MSK144SearchContext(Decoder):
+    """MSK144SearchContext(center_freq, search_width, search_step, scan_depth, nbadsync_threshold)
+    -- same argument order and meaning as msk_context.cuh:23."""
+
+    def __init__(self, center_freq: float, search_width: float, search_step: float, scan_depth: int,
+                 nbadsync_threshold: int, **kw):
+        super().__init__(center=center_freq, width=search_width, step=search_step, depth=scan_depth,
+                         thr=nbadsync_threshold, **kw)
+
+    def scanDepth(self) -> int:  # msk_context.cuh:160
+        return self.depth
+
+    def leftBound(self) -> float:  # msk_context.cuh:127
+        return self.left_hz
+
+    def rightBound(self) -> float:
+        return self.right_hz
+
+    def getNBadSyncThreshold(self) -> int:
+        return int(self.cfg.nbadsync_threshold)
+
+
+def do_decode(ctx: MSK144SearchContext, samples: np.ndarray, nchan: int = 1):
+    """main.cu:428-532 for every block of `samples` (raw stdin samples, not a pre-filtered block: the
+    front end runs on the GPU too).  Returns (lines, results)."""
+    return ctx.decode_host(samples, nchan)
+
+
+def decode_message(bits77: np.ndarray) -> Optional[str]:
+    """decode_softbits.cpp:23-55."""
+    b = np.ascontiguousarray(bits77, np.uint8)
+    buf = C.create_string_buffer(64)
+    ok = lib().msk144_decode_message(b.ctypes.data, buf)
+    return buf.value.decode("ascii") if ok else None
+
+
+def format_line(d: dict, date: Optional[str] = None) -> str:
+    """main.cu:406-419."""
+    l = Line()
+    l.snr, l.f0, l.num_avg, l.nbadsync, l.pattern_idx = d["snr"], d["f0"], d["num_avg"], d["nbadsync"], d["pattern_idx"]
+    l.text = d["text"].encode("ascii")
+    buf = C.create_string_buffer(256)
+    lib().msk144_format_line(C.byref(l), date.encode() if date else None, buf, 256)
+    return buf.value.decode("ascii")
+
+
+def reset_hash_tables():
+    lib().msk144_unpack77_reset()

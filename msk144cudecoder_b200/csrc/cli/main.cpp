@@ -1,0 +1,163 @@
+// msk144cudecoder -- command-line front of libmsk144b200.so.
+//
+// Same surface as the reference executable (main.cu:56-70,98-425): long options only, raw samples on
+// stdin (s16le mono 12 kHz, or interleaved s8 I,Q at 12 ksps), one decode line per distinct message
+// per block on stdout, a final "Done", banner and warnings on stderr, exit 0 at end of input.
+// Code defaults follow main.cu:124-133 (step 2, width 200, depth 4, method 2, threshold 1), not the
+// help text.  This program is a thin client of the C ABI: all GPU work happens in the library.
+#include <getopt.h>
+#include <unistd.h>
+
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <iostream>
+#include <string>
+#include <vector>
+
+#include "../../../include/msk144_b200.h"
+
+static void show_help(const char* prog) {
+    // clang-format off
+    std::cout << "Calling conversion: " << prog << " {[--help] | <options> }" << std::endl;
+    std::cout << " Where options are: " << std::endl;
+    std::cout << "                   --help                      Show this help and exit." << std::endl;
+    std::cout << "                   --center-frequency=1500.0   Center frequency in Hz." << std::endl;
+    std::cout << "                   --search-step=2.0           Search step in Hz. " << std::endl;
+    std::cout << "                   --search-width=100.0        Window in Hz around center frequency to find msk144 signal in." << std::endl;
+    std::cout << "                   --scan-depth=[1..8]         The more depth the more averagable patterns will be tried." << std::endl;
+    std::cout << "                   --read-mode=[1|2]           1=Audio,16 bit, mono, 12000sps, 1500Hz-recommended center; 2=IQ,8 bit, 12000sps, 0Hz-center. Default mode = 1." << std::endl;
+    std::cout << "                   --analytic-method=[1|2]     How to convert real signal to analytic quadrature signal. 1 = FFT; 2 = Shift-left + LPF + Shift-right. Default=2." << std::endl;
+    std::cout << "                   --nbadsync-threshold=[1..4] How many errors in sync pattern are acceptable to be passed to LDPC decoder." << std::endl;
+    std::cout << " Extensions of this build:" << std::endl;
+    std::cout << "                   --device=0                  CUDA device ordinal." << std::endl;
+    std::cout << "                   --batch-blocks=128          Blocks per GPU launch group when input arrives faster than real time." << std::endl;
+    std::cout << "                   --per-payload-text          Decode every payload's own text (the reference reuses the first decode of a block)." << std::endl;
+    // clang-format on
+}
+
+static const char* mode_string(int m) {
+    if (m == 1) return "Audio. 16 bits signed.";
+    if (m == 2) return "IQ. 8+8 bits.";
+    return "unknown";
+}
+
+int main(int argc, char* const argv[]) {
+    msk144_config cfg;
+    msk144_config_defaults(&cfg);
+    cfg.flags = MSK144_FLAG_COMPAT_DECODE_CACHE;
+    bool center_set = false;
+    static struct option long_options[] = {{"help", no_argument, 0, 0},                     // 0
+                                           {"center-frequency", required_argument, 0, 0},   // 1
+                                           {"search-step", required_argument, 0, 0},        // 2
+                                           {"search-width", required_argument, 0, 0},       // 3
+                                           {"scan-depth", required_argument, 0, 0},         // 4
+                                           {"read-mode", required_argument, 0, 0},          // 5
+                                           {"analytic-method", required_argument, 0, 0},    // 6
+                                           {"nbadsync-threshold", required_argument, 0, 0}, // 7
+                                           {"device", required_argument, 0, 0},             // 8
+                                           {"batch-blocks", required_argument, 0, 0},       // 9
+                                           {"per-payload-text", no_argument, 0, 0},         // 10
+                                           {0, 0, 0, 0}};
+    while (true) {
+        int option_index = 0;
+        const int c = getopt_long(argc, argv, "", long_options, &option_index);
+        if (c == -1) break;
+        if (c != 0) continue;  // unknown option: getopt already complained on stderr (main.cu:145-189)
+        switch (option_index) {
+            case 0: show_help(argv[0]); return 0;
+            case 1: cfg.center_frequency_hz = static_cast<float>(atof(optarg)); center_set = true; break;
+            case 2: cfg.search_step_hz = static_cast<float>(atof(optarg)); break;
+            case 3: cfg.search_width_hz = static_cast<float>(atof(optarg)); break;
+            case 4: cfg.scan_depth = atoi(optarg); break;
+            case 5: cfg.read_mode = atoi(optarg); break;
+            case 6: cfg.analytic_method = atoi(optarg); break;
+            case 7: cfg.nbadsync_threshold = atoi(optarg); break;
+            case 8: cfg.device = atoi(optarg); break;
+            case 9: cfg.max_batch_blocks = atoi(optarg); break;
+            case 10: cfg.flags &= ~MSK144_FLAG_COMPAT_DECODE_CACHE; break;
+            default: show_help(argv[0]); return 0;
+        }
+    }
+    if (!center_set) {  // main.cu:193-208
+        if (cfg.read_mode == 1) cfg.center_frequency_hz = 1500.0f;
+        else if (cfg.read_mode == 2) cfg.center_frequency_hz = 0.0f;
+        else {
+            std::cerr << "Wrong read mode " << cfg.read_mode << std::endl;
+            return 2;
+        }
+    }
+    msk144_decoder* dec = nullptr;
+    if (msk144_create(&cfg, &dec) != MSK144_OK) {
+        std::cerr << msk144_last_error() << std::endl;
+        return 2;
+    }
+    msk144_info info;
+    msk144_get_info(dec, &info);
+    // main.cu:233-252
+    std::cerr << "Actual parameters:" << std::endl
+              << "Center Frequency: " << cfg.center_frequency_hz << "Hz" << std::endl
+              << "Search Step: " << cfg.search_step_hz << "Hz" << std::endl
+              << "Search Width: " << cfg.search_width_hz << "Hz" << std::endl
+              << "Scan Depth: " << info.scan_depth << std::endl
+              << "Left Boundary: " << info.left_hz << "Hz" << std::endl
+              << "Right Boundary: " << info.right_hz << "Hz" << std::endl
+              << "Read Mode: (" << mode_string(cfg.read_mode) << ")" << std::endl;
+    if (cfg.read_mode == 1) std::cerr << "Analytic Method: " << cfg.analytic_method << std::endl;
+    std::cerr << "Badsync Threshold: " << cfg.nbadsync_threshold << std::endl
+              << "Frequency hypotheses: " << info.num_freqs << std::endl
+              << "Candidates per block: " << info.items_per_block << std::endl
+              << "GPU SMs: " << info.sm_count << std::endl
+              << std::endl;
+
+    const size_t hop_bytes = MSK144_HOP_SAMPLES * 2;  // both modes: 2 bytes per sample
+    const size_t block_bytes = MSK144_BLOCK_SAMPLES * 2;
+    std::vector<unsigned char> buf(hop_bytes * static_cast<size_t>(cfg.max_batch_blocks > 0 ? cfg.max_batch_blocks : 128));
+    std::vector<msk144_line> lines(4096);
+    size_t total_bytes = 0;
+    int rc_exit = 0;
+    while (true) {
+        // read() returns what is available: real-time input is processed block by block, a file or a
+        // fast pipe is processed in large launch groups.
+        const ssize_t n = read(0, buf.data(), buf.size());
+        if (n < 0) {
+            perror("read");
+            rc_exit = 2;
+            break;
+        }
+        if (n == 0) break;
+        total_bytes += static_cast<size_t>(n);
+        const auto t0 = std::chrono::steady_clock::now();
+        const int64_t before = 0;
+        (void)before;
+        if (msk144_push(dec, buf.data(), static_cast<size_t>(n)) != MSK144_OK) {
+            std::cerr << msk144_last_error() << std::endl;
+            rc_exit = 2;
+            break;
+        }
+        size_t got = 0;
+        do {
+            msk144_poll(dec, lines.data(), lines.size(), &got);
+            for (size_t i = 0; i < got; i++) {
+                char out[256];
+                msk144_format_line(&lines[i], nullptr, out, sizeof(out));
+                std::cout << out << std::endl;
+            }
+        } while (got == lines.size());
+        const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
+        const double blocks_in = static_cast<double>(n) / hop_bytes;
+        if (blocks_in >= 1.0 && ms > 210.0 * blocks_in)  // main.cu:397-403, scaled to the group size
+            std::cerr << "Warning: Working loop takes too much time: " << ms << " ms"
+                      << " of " << 210.0 * blocks_in << " ms max." << std::endl;
+    }
+    // main.cu:274-278,289-293: the final short fread ends the loop
+    size_t leftover;
+    if (total_bytes < block_bytes) leftover = total_bytes;
+    else leftover = (total_bytes - block_bytes) % hop_bytes;
+    const size_t rc_items = (cfg.read_mode == 1) ? leftover / 2 : leftover;
+    std::cerr << "Incomplete read error. rc=" << rc_items << std::endl;
+    std::cout << "Done" << std::endl;
+    msk144_destroy(dec);
+    return rc_exit;
+}

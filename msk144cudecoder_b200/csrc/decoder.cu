@@ -1,0 +1,798 @@
+// decoder.cu -- host orchestration and C ABI of libmsk144b200.so (include/msk144_b200.h).
+//
+// One decoder = one GPU + one stream.  A launch group is up to max_batch_blocks blocks (of one stream
+// or of many channels):  frontend_kernel -> scan_kernel -> ldpc_kernel, then two small D2H copies
+// (counters + SNR powers, then the compact list of LDPC successes).  The host then replays what
+// main.cu:480-525 and result_filter.cpp do per block.  There is no CPU fallback for any GPU stage.
+#include "../../include/msk144_b200.h"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <deque>
+#include <string>
+#include <vector>
+
+#include "host/postproc.h"
+#include "host/unpack77.h"
+#include "kernels.cuh"
+#include "ldpc_code.h"
+
+using namespace msk;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& what) {
+    g_err = what;
+    return code;
+}
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess)                                                                     \
+            return fail(MSK144_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_));         \
+    } while (0)
+
+struct Grid {  // msk_context.cuh:95-113
+    int nf;
+    float if1;
+};
+Grid make_grid(float width, float step) {
+    const float half_len_in_hz = width / 2;
+    const float half_len_cnt = half_len_in_hz / step;
+    const int half_len = static_cast<int>(half_len_cnt);
+    Grid g;
+    g.nf = half_len * 2 + 1;
+    g.if1 = -1 * half_len * step;
+    return g;
+}
+
+void build_tables(DevTables* t) {
+    std::memset(t, 0, sizeof(*t));
+    const float pi = 3.141592654f;  // CUDART_PI_F
+    for (size_t i = 0; i < 12; i++) {
+        const float angle = i * pi / 12.0f;  // msk_context.cuh:137-145
+        t->pp[i] = sinf(angle);
+    }
+    const int s8_org[8] = {0, 1, 1, 1, 0, 0, 1, 0};  // msk_context.cuh:149
+    for (int i = 0; i < 8; i++) t->s8[i] = static_cast<float>(2 * s8_org[i] - 1);
+    const int masks[8][6] = {{1, 0, 0, 0, 0, 0}, {1, 1, 0, 0, 0, 0}, {1, 1, 1, 0, 0, 0}, {1, 1, 1, 1, 0, 0},
+                             {1, 1, 1, 1, 1, 0}, {1, 1, 1, 1, 1, 1}, {1, 0, 0, 1, 0, 0}, {1, 0, 0, 1, 1, 0}};
+    for (int p = 0; p < 8; p++) {
+        int m = 0, w = 0;
+        for (int i = 0; i < 6; i++)
+            if (masks[p][i]) m |= 1 << i, w++;
+        t->mask[p] = static_cast<unsigned char>(m);
+        t->num_avg[p] = static_cast<unsigned char>(w);
+    }
+    int cnt[128] = {0};
+    for (int c = 0; c < 38; c++) {
+        int nrw = 0;
+        for (int s = 0; s < 11; s++)
+            if (MSK144_NM[c][s] >= 0) nrw++;
+        for (int s = 0; s < nrw; s++) {
+            const int b = MSK144_NM[c][s];
+            t->edge[b][cnt[b]++] = static_cast<unsigned short>(c | (s << 6) | (nrw << 10));
+            t->chkmask[c][b >> 5] |= 1u << (b & 31);
+        }
+    }
+    // x^(95-k) mod (x^13 + 0x15D7): contribution of message bit k to the CRC (ldpc_kernel.cuh:32-63)
+    for (int k = 0; k < 77; k++) {
+        unsigned rem = 0;
+        for (int i = 0; i < 96; i++) {
+            rem = (rem << 1) | (i == k ? 1u : 0u);
+            if (rem & 0x2000u) rem ^= 0x2000u | 0x15D7u;
+        }
+        t->crc_r[k] = static_cast<unsigned short>(rem & 0x1fffu);
+    }
+}
+
+struct RawResult {
+    int64_t gblock;
+    ResultRec r;
+};
+
+}  // namespace
+
+struct msk144_decoder {
+    msk144_config cfg{};
+    int nf = 0, depth = 0, items = 0, sm_count = 0;
+    float if1 = 0.f;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+    // device capacity (blocks per launch group)
+    int cap_blocks = 0;
+    float2* d_blocks = nullptr;
+    float* d_powers = nullptr;
+    CandRec* d_cands = nullptr;
+    QueueRec* d_queue = nullptr;
+    ResultRec* d_results = nullptr;
+    int* d_counters = nullptr;  // [0] queue count, [1] result count
+    size_t queue_cap = 0, result_cap = 0;
+    void* d_raw = nullptr;
+    size_t d_raw_bytes = 0;
+    float2* d_twiddle = nullptr;
+    float* d_hfilt = nullptr;
+
+    int* h_counters = nullptr;  // pinned
+    float* h_powers = nullptr;  // pinned [cap][8]
+    ResultRec* h_results = nullptr;
+    size_t h_results_cap = 0;
+
+    // accumulated by the last decode call
+    msk144_stage_times times{};
+    int64_t launches = 0;
+
+    // streaming state (msk144_push / msk144_poll)
+    std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
+    int64_t next_block = 0;
+    mskhost::SnrTracker stream_snr;
+    std::deque<msk144_line> out_lines;
+
+    ~msk144_decoder() { release(); }
+    void release();
+    int ensure_capacity(int nblocks);
+    int ensure_raw(size_t bytes);
+    int ensure_host_results(size_t n);
+    int launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
+    int fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
+    int decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
+                      mskhost::SnrTracker* carry, std::vector<msk144_line>* lines, std::vector<msk144_result>* results);
+};
+
+void msk144_decoder::release() {
+    cudaSetDevice(cfg.device);
+    cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
+    cudaFree(d_counters), cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt);
+    d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
+    d_counters = nullptr, d_raw = nullptr, d_twiddle = nullptr, d_hfilt = nullptr;
+    if (h_counters) cudaFreeHost(h_counters);
+    if (h_powers) cudaFreeHost(h_powers);
+    if (h_results) cudaFreeHost(h_results);
+    h_counters = nullptr, h_powers = nullptr, h_results = nullptr;
+    for (auto& e : ev)
+        if (e) cudaEventDestroy(e), e = nullptr;
+    if (stream) cudaStreamDestroy(stream), stream = nullptr;
+    cap_blocks = 0;
+}
+
+int msk144_decoder::ensure_capacity(int nblocks) {
+    if (nblocks <= cap_blocks) return 0;
+    cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
+    d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
+    if (h_powers) cudaFreeHost(h_powers), h_powers = nullptr;
+    cap_blocks = 0;
+    const size_t nb = static_cast<size_t>(nblocks);
+    queue_cap = nb * items;  // worst case: every candidate passes the sync gate
+    result_cap = nb * items;
+    if (queue_cap > 0x7fffffffull) return fail(MSK144_EINVAL, "batch too large");
+    CK(cudaMalloc(&d_blocks, nb * N * sizeof(float2)));
+    CK(cudaMalloc(&d_powers, nb * 8 * sizeof(float)));
+    CK(cudaMalloc(&d_cands, nb * items * sizeof(CandRec)));
+    CK(cudaMalloc(&d_queue, queue_cap * sizeof(QueueRec)));
+    CK(cudaMalloc(&d_results, result_cap * sizeof(ResultRec)));
+    CK(cudaMallocHost(&h_powers, nb * 8 * sizeof(float)));
+    cap_blocks = nblocks;
+    return 0;
+}
+
+int msk144_decoder::ensure_raw(size_t bytes) {
+    if (bytes <= d_raw_bytes) return 0;
+    cudaFree(d_raw);
+    d_raw = nullptr, d_raw_bytes = 0;
+    CK(cudaMalloc(&d_raw, bytes));
+    d_raw_bytes = bytes;
+    return 0;
+}
+
+int msk144_decoder::ensure_host_results(size_t n) {
+    if (n <= h_results_cap) return 0;
+    if (h_results) cudaFreeHost(h_results), h_results = nullptr;
+    h_results_cap = 0;
+    size_t want = std::max<size_t>(n, 4096);
+    want += want / 2;
+    CK(cudaMallocHost(&h_results, want * sizeof(ResultRec)));
+    h_results_cap = want;
+    return 0;
+}
+
+int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
+                                 cudaStream_t st) {
+    CK(cudaMemsetAsync(d_counters, 0, 4 * sizeof(int), st));
+    CK(cudaEventRecord(ev[0], st));
+    if (cfg.read_mode == 1 && cfg.analytic_method == 1) {
+        FftParams fp;
+        fp.raw = static_cast<const short*>(d_in);
+        fp.chan_stride = chan_stride;
+        fp.bpc = bpc;
+        fp.block0 = block0;
+        fp.twiddle = d_twiddle;
+        fp.hfilt = d_hfilt;
+        fp.out = d_blocks;
+        fp.powers = d_powers;
+        fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, st>>>(fp);
+    } else {
+        FrontParams fp;
+        fp.raw = d_in;
+        fp.chan_stride = chan_stride;
+        fp.bpc = bpc;
+        fp.read_mode = cfg.read_mode;
+        fp.block0 = block0;
+        fp.out = d_blocks;
+        fp.powers = d_powers;
+        frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, st>>>(fp);
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[1], st));
+    ScanParams sp;
+    sp.blocks = d_blocks;
+    sp.nf = nf;
+    sp.depth = depth;
+    sp.thr = cfg.nbadsync_threshold;
+    sp.fpc = std::max(1, std::min(8, static_cast<int>((static_cast<long long>(nf) * nb) / (sm_count * 8))));
+    sp.center = cfg.center_frequency_hz;
+    sp.if1 = if1;
+    sp.step = cfg.search_step_hz;
+    sp.block0 = 0;
+    sp.cands = d_cands;
+    sp.queue = d_queue;
+    sp.queue_count = d_counters;
+    sp.queue_cap = static_cast<int>(std::min<size_t>(queue_cap, static_cast<size_t>(nb) * items));
+    dim3 sgrid((nf + sp.fpc - 1) / sp.fpc, nb);
+    scan_kernel<<<sgrid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[2], st));
+    LdpcParams lp{};
+    lp.llr = reinterpret_cast<const float*>(d_queue) + 8;
+    lp.stride = sizeof(QueueRec) / sizeof(float);
+    lp.count_ptr = d_counters;
+    lp.count = 0;
+    lp.cap = sp.queue_cap;
+    lp.queue = d_queue;
+    lp.results = d_results;
+    lp.result_count = d_counters + 1;
+    lp.result_cap = static_cast<int>(std::min<size_t>(result_cap, 0x7fffffffull));
+    lp.flat_out = nullptr;
+    ldpc_kernel<<<sm_count * 8, LDPC_WARPS * 32, 0, st>>>(lp);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ev[3], st));
+    launches += 3;
+    return 0;
+}
+
+int msk144_decoder::fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0,
+                                std::vector<float>* powers) {
+    CK(cudaMemcpyAsync(h_counters, d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(h_powers, d_powers, static_cast<size_t>(nb) * 8 * sizeof(float), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const int qn = h_counters[0], rn = h_counters[1];
+    if (static_cast<size_t>(qn) > queue_cap || static_cast<size_t>(rn) > result_cap)
+        return fail(MSK144_EOVERFLOW, "device queue overflow");
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev[0], ev[1]), times.frontend_ms += ms;
+    cudaEventElapsedTime(&ms, ev[1], ev[2]), times.scan_ms += ms;
+    cudaEventElapsedTime(&ms, ev[2], ev[3]), times.ldpc_ms += ms;
+    cudaEventElapsedTime(&ms, ev[0], ev[3]), times.total_ms += ms;
+    times.blocks += nb;
+    times.llr_codewords += qn;
+    times.ldpc_successes += rn;
+    if (powers) powers->insert(powers->end(), h_powers, h_powers + static_cast<size_t>(nb) * 8);
+    if (rn > 0) {
+        if (int rc = ensure_host_results(rn)) return rc;
+        CK(cudaMemcpyAsync(h_results, d_results, static_cast<size_t>(rn) * sizeof(ResultRec), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        if (out)
+            for (int i = 0; i < rn; i++) out->push_back(RawResult{gblock0 + h_results[i].block, h_results[i]});
+    }
+    return 0;
+}
+
+int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
+                                  mskhost::SnrTracker* carry, std::vector<msk144_line>* lines,
+                                  std::vector<msk144_result>* results) {
+    times = msk144_stage_times{};
+    const int64_t bpc = spc >= static_cast<size_t>(N) ? static_cast<int64_t>((spc - N) / (N / 2)) + 1 : 0;
+    const int64_t total = bpc * nchan;
+    if (total == 0) return 0;
+    if (bpc > 0x7fffffff) return fail(MSK144_EINVAL, "channel too long for one call");
+    const int group = std::max(1, cfg.max_batch_blocks);
+    if (int rc = ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
+    std::vector<RawResult> raw;
+    std::vector<float> powers;
+    powers.reserve(static_cast<size_t>(total) * 8);
+    for (int64_t g0 = 0; g0 < total; g0 += group) {
+        const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
+        if (int rc = launch_group(d_in, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
+        if (int rc = fetch_group(nb, st, &raw, g0, &powers)) return rc;
+    }
+    times.kernel_launches = launches;
+    // ---- host post-processing, block by block in stream order (main.cu:388-419) ----
+    std::sort(raw.begin(), raw.end(), [](const RawResult& a, const RawResult& b) {
+        if (a.gblock != b.gblock) return a.gblock < b.gblock;
+        return a.r.item < b.r.item;
+    });
+    const bool compat = (cfg.flags & MSK144_FLAG_COMPAT_DECODE_CACHE) != 0;
+    size_t ri = 0;
+    for (int ch = 0; ch < nchan; ch++) {
+        mskhost::SnrTracker local;
+        mskhost::SnrTracker* snr = (carry && nchan == 1) ? carry : &local;
+        for (int64_t k = 0; k < bpc; k++) {
+            const int64_t gb = static_cast<int64_t>(ch) * bpc + k;
+            snr->process_powers(&powers[static_cast<size_t>(gb) * 8]);
+            std::vector<mskhost::Present> present;
+            while (ri < raw.size() && raw[ri].gblock == gb) {
+                const ResultRec& r = raw[ri].r;
+                mskhost::Present p;
+                p.item = r.item;
+                p.f0 = r.f0;
+                p.pattern_idx = static_cast<int>((r.item / NCAND) % depth);
+                p.num_avg = 0;
+                {
+                    static const int navg[8] = {1, 2, 3, 4, 5, 6, 2, 3};
+                    p.num_avg = navg[p.pattern_idx];
+                }
+                p.nbadsync = r.nbadsync;
+                std::memset(p.message, 0, sizeof(p.message));
+                for (int b = 0; b < 77; b++) p.message[b] = (r.bits[b >> 5] >> (b & 31)) & 1u;
+                present.push_back(p);
+                if (results) {
+                    msk144_result o;
+                    std::memset(&o, 0, sizeof(o));
+                    o.block_index = block_index_base + k;
+                    o.channel = ch;
+                    o.item_index = r.item;
+                    o.freq_idx = r.item / (NCAND * depth);
+                    o.pattern_idx = p.pattern_idx;
+                    o.slot = r.item % NCAND;
+                    o.pos = r.pos;
+                    o.f0 = r.f0;
+                    o.xb = r.xb;
+                    o.num_avg = p.num_avg;
+                    o.nbadsync = r.nbadsync;
+                    o.ldpc_iters = r.iters;
+                    o.ldpc_nhard = r.nhard;
+                    std::memcpy(o.message, p.message, 80);
+                    results->push_back(o);
+                }
+                ri++;
+            }
+            if (lines && !present.empty()) {
+                const auto bl = mskhost::block_lines(present, compat, snr->snr_i());
+                for (const auto& l : bl) {
+                    msk144_line o;
+                    std::memset(&o, 0, sizeof(o));
+                    o.block_index = block_index_base + k;
+                    o.channel = ch;
+                    o.snr = l.snr;
+                    o.f0 = l.f0;
+                    o.num_avg = l.num_avg;
+                    o.nbadsync = l.nbadsync;
+                    o.pattern_idx = l.pattern_idx;
+                    std::memcpy(o.payload, l.payload, 80);
+                    std::snprintf(o.text, sizeof(o.text), "%s", l.message.c_str());
+                    lines->push_back(o);
+                }
+            }
+        }
+    }
+    return 0;
+}
+
+// ========================================================================================= C ABI
+extern "C" {
+
+const char* msk144_last_error(void) { return g_err.c_str(); }
+
+void msk144_config_defaults(msk144_config* cfg) {
+    if (!cfg) return;
+    std::memset(cfg, 0, sizeof(*cfg));
+    cfg->center_frequency_hz = 1500.0f;  // main.cu:125
+    cfg->search_step_hz = 2.0f;          // main.cu:129
+    cfg->search_width_hz = 200.0f;       // main.cu:130
+    cfg->scan_depth = 4;                 // main.cu:131
+    cfg->read_mode = 1;
+    cfg->analytic_method = 2;            // main.cu:132
+    cfg->nbadsync_threshold = 1;         // main.cu:133
+    cfg->device = 0;
+    cfg->max_batch_blocks = 128;
+    cfg->flags = 0;
+}
+
+int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
+    if (!cfg || !out) return fail(MSK144_EINVAL, "null argument");
+    *out = nullptr;
+    if (!(cfg->search_step_hz > 0.0f)) return fail(MSK144_EINVAL, "search step must be > 0");  // msk_context.cuh:97
+    if (cfg->read_mode != 1 && cfg->read_mode != 2) return fail(MSK144_EINVAL, "read mode must be 1 or 2");
+    if (cfg->read_mode == 1 && cfg->analytic_method != 1 && cfg->analytic_method != 2)
+        return fail(MSK144_EINVAL, "analytic method must be 1 or 2");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(MSK144_ENODEV, "no CUDA device: this library has no CPU path");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(MSK144_EINVAL, "bad device ordinal");
+    CK(cudaSetDevice(cfg->device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major < 10)
+        return fail(MSK144_ENODEV, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+                                       ": kernels are built for sm_100a only");
+    msk144_decoder* d = new msk144_decoder();
+    d->cfg = *cfg;
+    if (d->cfg.max_batch_blocks <= 0) d->cfg.max_batch_blocks = 128;
+    d->depth = std::max(1, std::min(8, cfg->scan_depth));  // msk_context.cuh:28-33
+    const Grid g = make_grid(cfg->search_width_hz, cfg->search_step_hz);
+    d->nf = g.nf;
+    d->if1 = g.if1;
+    d->items = d->nf * d->depth * NCAND;
+    d->sm_count = prop.multiProcessorCount;
+    auto bail = [&](int rc) {
+        delete d;
+        return rc;
+    };
+#define CKD(call)                                                                                          \
+    do {                                                                                                   \
+        cudaError_t e_ = (call);                                                                           \
+        if (e_ != cudaSuccess) return bail(fail(MSK144_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_))); \
+    } while (0)
+    CKD(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    for (auto& e : d->ev) CKD(cudaEventCreate(&e));
+    DevTables tab;
+    build_tables(&tab);
+    CKD(cudaMemcpyToSymbol(c_tab, &tab, sizeof(tab)));
+    CKD(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
+    CKD(cudaFuncSetAttribute(fft_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FFT_SMEM)));
+    CKD(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
+    CKD(cudaMalloc(&d->d_counters, 4 * sizeof(int)));
+    CKD(cudaMallocHost(&d->h_counters, 4 * sizeof(int)));
+    if (cfg->read_mode == 1 && cfg->analytic_method == 1) {
+        // analytic_fft.cu:32-58: raised-cosine band-pass, 1500 +- 1000 Hz, beta 0.1; DC halved, upper half zero
+        std::vector<float2> tw(NFFT / 2);
+        for (int k = 0; k < NFFT / 2; k++) {
+            const double a = -2.0 * M_PI * k / NFFT;
+            tw[k] = make_float2(static_cast<float>(std::cos(a)), static_cast<float>(std::sin(a)));
+        }
+        std::vector<float> h(NFFT, 0.0f);
+        const float df = 12000.0f / NFFT;
+        const float pi = 3.141592654f;
+        const float t = 1.0f / 2000.0f, beta = 0.1f;
+        for (int i = 0; i < NFFT / 2; i++) {
+            const float ff = i * df;
+            const float f = ff - 1500.0f;
+            h[i] = 1.0f;
+            if (fabsf(f) > (1 - beta) / (2 * t) && fabsf(f) <= (1 + beta) / (2 * t))
+                h[i] = h[i] * 0.5f * (1.0f + cosf((pi * t / beta) * (fabsf(f) - (1 - beta) / (2 * t))));
+            else if (fabsf(f) > (1 + beta) / (2 * t))
+                h[i] = 0;
+        }
+        h[0] = 0.5f * h[0];
+        CKD(cudaMalloc(&d->d_twiddle, tw.size() * sizeof(float2)));
+        CKD(cudaMalloc(&d->d_hfilt, h.size() * sizeof(float)));
+        CKD(cudaMemcpy(d->d_twiddle, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice));
+        CKD(cudaMemcpy(d->d_hfilt, h.data(), h.size() * sizeof(float), cudaMemcpyHostToDevice));
+    }
+#undef CKD
+    *out = d;
+    return MSK144_OK;
+}
+
+void msk144_destroy(msk144_decoder* dec) { delete dec; }
+
+int msk144_get_info(const msk144_decoder* dec, msk144_info* info) {
+    if (!dec || !info) return fail(MSK144_EINVAL, "null argument");
+    std::memset(info, 0, sizeof(*info));
+    info->num_freqs = dec->nf;
+    info->scan_depth = dec->depth;
+    info->items_per_block = dec->items;
+    info->sm_count = dec->sm_count;
+    info->left_hz = dec->cfg.center_frequency_hz + dec->if1;  // msk_context.cuh:127-129
+    info->right_hz = dec->cfg.center_frequency_hz + dec->if1 + (dec->nf - 1) * dec->cfg.search_step_hz;
+    info->max_batch_blocks = dec->cfg.max_batch_blocks;
+    return MSK144_OK;
+}
+
+int msk144_get_stage_times(const msk144_decoder* dec, msk144_stage_times* t) {
+    if (!dec || !t) return fail(MSK144_EINVAL, "null argument");
+    *t = dec->times;
+    t->kernel_launches = dec->launches;
+    return MSK144_OK;
+}
+
+static void copy_out(const std::vector<msk144_line>& lv, const std::vector<msk144_result>& rv, msk144_line* lines,
+                     size_t line_cap, size_t* nlines, msk144_result* results, size_t result_cap, size_t* nresults,
+                     int* rc) {
+    if (nlines) *nlines = lv.size();
+    if (nresults) *nresults = rv.size();
+    if (lines) std::memcpy(lines, lv.data(), std::min(line_cap, lv.size()) * sizeof(msk144_line));
+    if (results) std::memcpy(results, rv.data(), std::min(result_cap, rv.size()) * sizeof(msk144_result));
+    if ((lines && lv.size() > line_cap) || (results && rv.size() > result_cap))
+        *rc = fail(MSK144_EOVERFLOW, "output array too small");
+}
+
+int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t spc, int nchan, void* stream,
+                         msk144_line* lines, size_t line_cap, size_t* nlines, msk144_result* results,
+                         size_t result_cap, size_t* nresults) {
+    if (!dec || !d_samples || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : dec->stream;
+    std::vector<msk144_line> lv;
+    std::vector<msk144_result> rv;
+    if (int rc = dec->decode_common(d_samples, spc, nchan, st, 0, nullptr, &lv, results || nresults ? &rv : nullptr))
+        return rc;
+    int rc = MSK144_OK;
+    copy_out(lv, rv, lines, line_cap, nlines, results, result_cap, nresults, &rc);
+    return rc;
+}
+
+int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int nchan, msk144_line* lines,
+                       size_t line_cap, size_t* nlines, msk144_result* results, size_t result_cap, size_t* nresults) {
+    if (!dec || !samples || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    const size_t bytes = spc * static_cast<size_t>(nchan) * 2;  // s16 mono or s8 I + s8 Q: 2 bytes per sample
+    if (int rc = dec->ensure_raw(bytes)) return rc;
+    CK(cudaMemcpyAsync(dec->d_raw, samples, bytes, cudaMemcpyHostToDevice, dec->stream));
+    return msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results, result_cap,
+                                nresults);
+}
+
+int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, int nchan, void* stream,
+                      int64_t* nblocks_out) {
+    if (!dec || !d_samples || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : dec->stream;
+    const int64_t bpc = spc >= static_cast<size_t>(N) ? static_cast<int64_t>((spc - N) / (N / 2)) + 1 : 0;
+    const int64_t total = bpc * nchan;
+    if (nblocks_out) *nblocks_out = total;
+    if (total == 0) return MSK144_OK;
+    const int group = std::max(1, dec->cfg.max_batch_blocks);
+    if (int rc = dec->ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
+    for (int64_t g0 = 0; g0 < total; g0 += group) {
+        const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
+        if (int rc = dec->launch_group(d_samples, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
+    }
+    return MSK144_OK;
+}
+
+// ---- streaming -----------------------------------------------------------------------------------
+int msk144_reset_stream(msk144_decoder* dec) {
+    if (!dec) return fail(MSK144_EINVAL, "null argument");
+    dec->pending.clear();
+    dec->next_block = 0;
+    dec->stream_snr.reset();
+    dec->out_lines.clear();
+    return MSK144_OK;
+}
+
+int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
+    if (!dec || (!bytes && nbytes)) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    const uint8_t* b = static_cast<const uint8_t*>(bytes);
+    dec->pending.insert(dec->pending.end(), b, b + nbytes);
+    const size_t nsamp = dec->pending.size() / 2;
+    if (nsamp < static_cast<size_t>(N)) return MSK144_OK;
+    const size_t nblocks = (nsamp - N) / (N / 2) + 1;
+    const size_t used_samples = (nblocks - 1) * (N / 2) + N;
+    if (int rc = dec->ensure_raw(used_samples * 2)) return rc;
+    CK(cudaMemcpyAsync(dec->d_raw, dec->pending.data(), used_samples * 2, cudaMemcpyHostToDevice, dec->stream));
+    std::vector<msk144_line> lv;
+    if (int rc = dec->decode_common(dec->d_raw, used_samples, 1, dec->stream, dec->next_block, &dec->stream_snr, &lv,
+                                    nullptr))
+        return rc;
+    for (const auto& l : lv) dec->out_lines.push_back(l);
+    dec->next_block += static_cast<int64_t>(nblocks);
+    // keep the second half of the last block: it is the first half of the next one (main.cu:284-288)
+    dec->pending.erase(dec->pending.begin(), dec->pending.begin() + nblocks * (N / 2) * 2);
+    return MSK144_OK;
+}
+
+int msk144_poll(msk144_decoder* dec, msk144_line* lines, size_t cap, size_t* nlines) {
+    if (!dec || !nlines) return fail(MSK144_EINVAL, "null argument");
+    size_t n = 0;
+    while (n < cap && !dec->out_lines.empty()) {
+        lines[n++] = dec->out_lines.front();
+        dec->out_lines.pop_front();
+    }
+    *nlines = n;
+    return MSK144_OK;
+}
+
+// ---- stage level -----------------------------------------------------------------------------------
+int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsamples, float* blocks_re_im,
+                         float* powers8, int64_t* nblocks_out) {
+    if (!dec || !samples) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    const int64_t total = nsamples >= static_cast<size_t>(N) ? static_cast<int64_t>((nsamples - N) / (N / 2)) + 1 : 0;
+    if (nblocks_out) *nblocks_out = total;
+    if (total == 0) return MSK144_OK;
+    if (int rc = dec->ensure_raw(nsamples * 2)) return rc;
+    CK(cudaMemcpyAsync(dec->d_raw, samples, nsamples * 2, cudaMemcpyHostToDevice, dec->stream));
+    const int group = std::max(1, dec->cfg.max_batch_blocks);
+    if (int rc = dec->ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
+    // run only the front-end kernel of each group
+    for (int64_t g0 = 0; g0 < total; g0 += group) {
+        const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
+        if (dec->cfg.read_mode == 1 && dec->cfg.analytic_method == 1) {
+            FftParams fp;
+            fp.raw = static_cast<const short*>(dec->d_raw);
+            fp.chan_stride = static_cast<long long>(nsamples);
+            fp.bpc = static_cast<int>(total);
+            fp.block0 = g0;
+            fp.twiddle = dec->d_twiddle;
+            fp.hfilt = dec->d_hfilt;
+            fp.out = dec->d_blocks;
+            fp.powers = dec->d_powers;
+            fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, dec->stream>>>(fp);
+        } else {
+            FrontParams fp;
+            fp.raw = dec->d_raw;
+            fp.chan_stride = static_cast<long long>(nsamples);
+            fp.bpc = static_cast<int>(total);
+            fp.read_mode = dec->cfg.read_mode;
+            fp.block0 = g0;
+            fp.out = dec->d_blocks;
+            fp.powers = dec->d_powers;
+            frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, dec->stream>>>(fp);
+        }
+        CK(cudaGetLastError());
+        dec->launches += 1;
+        if (blocks_re_im)
+            CK(cudaMemcpyAsync(blocks_re_im + static_cast<size_t>(g0) * N * 2, dec->d_blocks,
+                               static_cast<size_t>(nb) * N * sizeof(float2), cudaMemcpyDeviceToHost, dec->stream));
+        if (powers8)
+            CK(cudaMemcpyAsync(powers8 + static_cast<size_t>(g0) * 8, dec->d_powers, static_cast<size_t>(nb) * 8 * sizeof(float),
+                               cudaMemcpyDeviceToHost, dec->stream));
+        CK(cudaStreamSynchronize(dec->stream));
+    }
+    return MSK144_OK;
+}
+
+int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nblocks, msk144_candidate* cands,
+                     float* llr, uint32_t* llr_item, size_t llr_cap, size_t* nllr) {
+    if (!dec || !blocks_re_im || nblocks < 1) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    const int group = std::max(1, dec->cfg.max_batch_blocks);
+    if (int rc = dec->ensure_capacity(static_cast<int>(std::min<int64_t>(group, nblocks)))) return rc;
+    size_t total_llr = 0;
+    int rc_out = MSK144_OK;
+    std::vector<QueueRec> hq;
+    for (int64_t g0 = 0; g0 < nblocks; g0 += group) {
+        const int nb = static_cast<int>(std::min<int64_t>(group, nblocks - g0));
+        CK(cudaMemcpyAsync(dec->d_blocks, blocks_re_im + static_cast<size_t>(g0) * N * 2,
+                           static_cast<size_t>(nb) * N * sizeof(float2), cudaMemcpyHostToDevice, dec->stream));
+        CK(cudaMemsetAsync(dec->d_counters, 0, 4 * sizeof(int), dec->stream));
+        ScanParams sp;
+        sp.blocks = dec->d_blocks;
+        sp.nf = dec->nf;
+        sp.depth = dec->depth;
+        sp.thr = dec->cfg.nbadsync_threshold;
+        sp.fpc = std::max(1, std::min(8, static_cast<int>((static_cast<long long>(dec->nf) * nb) / (dec->sm_count * 8))));
+        sp.center = dec->cfg.center_frequency_hz;
+        sp.if1 = dec->if1;
+        sp.step = dec->cfg.search_step_hz;
+        sp.block0 = 0;
+        sp.cands = dec->d_cands;
+        sp.queue = dec->d_queue;
+        sp.queue_count = dec->d_counters;
+        sp.queue_cap = static_cast<int>(static_cast<size_t>(nb) * dec->items);
+        dim3 sgrid((dec->nf + sp.fpc - 1) / sp.fpc, nb);
+        scan_kernel<<<sgrid, SCAN_THREADS, SCAN_SMEM, dec->stream>>>(sp);
+        CK(cudaGetLastError());
+        dec->launches += 1;
+        CK(cudaMemcpyAsync(dec->h_counters, dec->d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, dec->stream));
+        if (cands)
+            CK(cudaMemcpyAsync(cands + static_cast<size_t>(g0) * dec->items, dec->d_cands,
+                               static_cast<size_t>(nb) * dec->items * sizeof(CandRec), cudaMemcpyDeviceToHost, dec->stream));
+        CK(cudaStreamSynchronize(dec->stream));
+        const int qn = dec->h_counters[0];
+        if (llr || llr_item) {
+            hq.resize(qn);
+            CK(cudaMemcpy(hq.data(), dec->d_queue, static_cast<size_t>(qn) * sizeof(QueueRec), cudaMemcpyDeviceToHost));
+            for (int i = 0; i < qn; i++) {
+                const size_t row = total_llr + i;
+                if (row >= llr_cap) {
+                    rc_out = MSK144_EOVERFLOW;
+                    continue;
+                }
+                if (llr) std::memcpy(llr + row * 128, hq[i].llr, 128 * sizeof(float));
+                if (llr_item) llr_item[row] = static_cast<uint32_t>((g0 + hq[i].block) * dec->items + hq[i].item);
+            }
+        }
+        if (cands) {  // make llr_slot global across groups
+            msk144_candidate* c = cands + static_cast<size_t>(g0) * dec->items;
+            for (size_t i = 0; i < static_cast<size_t>(nb) * dec->items; i++)
+                if (c[i].llr_slot >= 0) c[i].llr_slot += static_cast<int32_t>(total_llr);
+        }
+        total_llr += qn;
+    }
+    if (nllr) *nllr = total_llr;
+    if (rc_out != MSK144_OK) return fail(rc_out, "llr array too small");
+    return MSK144_OK;
+}
+
+int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t ncw, uint32_t* d_out, void* stream) {
+    if (!dec || !d_llr || !d_out) return fail(MSK144_EINVAL, "bad argument");
+    if (ncw > 0x7fffffffull) return fail(MSK144_EINVAL, "too many codewords for one call");
+    CK(cudaSetDevice(dec->cfg.device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : dec->stream;
+    LdpcParams lp{};
+    lp.llr = d_llr;
+    lp.stride = 128;
+    lp.count_ptr = nullptr;
+    lp.count = static_cast<int>(ncw);
+    lp.cap = static_cast<int>(ncw);
+    lp.flat_out = reinterpret_cast<uint4*>(d_out);
+    const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * 8, (ncw + LDPC_WARPS - 1) / LDPC_WARPS));
+    if (grid > 0) {
+        ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
+        CK(cudaGetLastError());
+        dec->launches += 1;
+    }
+    return MSK144_OK;
+}
+
+int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, uint8_t* found, uint8_t* msg77,
+                            int32_t* iters, int32_t* nhard) {
+    if (!dec || !llr) return fail(MSK144_EINVAL, "bad argument");
+    if (ncw == 0) return MSK144_OK;
+    CK(cudaSetDevice(dec->cfg.device));
+    float* d_llr = nullptr;
+    uint32_t* d_out = nullptr;
+    CK(cudaMalloc(&d_llr, ncw * 128 * sizeof(float)));
+    if (cudaMalloc(&d_out, ncw * 16) != cudaSuccess) {
+        cudaFree(d_llr);
+        return fail(MSK144_ENOMEM, "cudaMalloc");
+    }
+    int rc = MSK144_OK;
+    std::vector<uint32_t> out(ncw * 4);
+    do {
+        if (cudaMemcpyAsync(d_llr, llr, ncw * 128 * sizeof(float), cudaMemcpyHostToDevice, dec->stream) != cudaSuccess) {
+            rc = fail(MSK144_ECUDA, "H2D");
+            break;
+        }
+        rc = msk144_ldpc_decode_device(dec, d_llr, ncw, d_out, dec->stream);
+        if (rc) break;
+        if (cudaMemcpyAsync(out.data(), d_out, ncw * 16, cudaMemcpyDeviceToHost, dec->stream) != cudaSuccess ||
+            cudaStreamSynchronize(dec->stream) != cudaSuccess) {
+            rc = fail(MSK144_ECUDA, std::string("ldpc: ") + cudaGetErrorString(cudaGetLastError()));
+            break;
+        }
+    } while (0);
+    cudaFree(d_llr);
+    cudaFree(d_out);
+    if (rc) return rc;
+    for (size_t i = 0; i < ncw; i++) {
+        const uint32_t* w = &out[i * 4];
+        const bool f = (w[2] >> 31) != 0;
+        if (found) found[i] = f ? 1 : 0;
+        if (msg77)
+            for (int b = 0; b < 77; b++) msg77[i * 77 + b] = (w[b >> 5] >> (b & 31)) & 1u;
+        if (iters) iters[i] = static_cast<int32_t>(w[3] & 0xff);
+        if (nhard) {
+            const int nh = static_cast<int>((w[3] >> 8) & 0xff);
+            nhard[i] = (nh == 0xff) ? -1 : nh;
+        }
+    }
+    return MSK144_OK;
+}
+
+int msk144_decode_message(const uint8_t* msg77, char* text) {
+    std::string s;
+    const bool ok = mskhost::decode_message(msg77, &s);
+    if (text) std::snprintf(text, 38, "%s", s.c_str());
+    return ok ? 1 : 0;
+}
+
+int msk144_format_line(const msk144_line* line, const char* date14, char* out, size_t cap) {
+    if (!line || !out) return fail(MSK144_EINVAL, "null argument");
+    const std::string stamp = date14 ? std::string(date14) : mskhost::now_stamp();
+    const std::string s = mskhost::format_line(line->snr, line->f0, line->num_avg, line->nbadsync, line->pattern_idx,
+                                               stamp.c_str(), line->text);
+    std::snprintf(out, cap, "%s", s.c_str());
+    return static_cast<int>(s.size());
+}
+
+}  // extern "C"

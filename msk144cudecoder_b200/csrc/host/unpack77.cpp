@@ -305,7 +305,7 @@ bool unpack77_impl(const char* c77, int /*nrx*/, std::string* msg) {
             if (irpt >= 5) {
                 int isnr = irpt - 35;
                 if (isnr > 50) isnr -= 101;
-                char r[8];
+                char r[16];
                 std::snprintf(r, sizeof(r), "%c%02d", isnr < 0 ? '-' : '+', isnr < 0 ? -isnr : isnr);
                 *msg = c1 + " " + c2 + (ir ? " R" : " ") + r;
             }

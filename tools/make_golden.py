@@ -1,0 +1,124 @@
+#!/usr/bin/env python3
+"""Generate tests/golden/*.npz by running the REAL reference on a B200.
+
+Run on the GPU box (gpurun), after oracle/build_ref.sh has produced oracle/_ref/{ref_dump,
+msk144cudecoder_ref} in the CPU container.  Inputs are regenerated from seeds by
+msk144cudecoder_b200.synth, so only the reference's OUTPUTS are stored:
+
+  per case   items: pos, xb, nbadsync, present, iters, nhard, packed payload   (every candidate)
+             snr per block, the reference CLI's stdout lines (date masked)
+             filtered blocks and LLRs for a bounded subset (sizes kept small for git)
+
+Usage: python tools/make_golden.py <outdir>      (writes <outdir>/<case>.npz)
+"""
+import os
+import re
+import subprocess
+import sys
+import tempfile
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from msk144cudecoder_b200 import synth  # noqa: E402
+
+REF = os.path.join(ROOT, "oracle", "_ref")
+ITEM_DTYPE = np.dtype([("freq_idx", "<u4"), ("pattern_idx", "<u4"), ("pos", "<u4"), ("f0", "<f4"),
+                       ("nbadsync", "<i4"), ("xb", "<f4"), ("num_avg", "<i4"), ("llr", "<f4", (128,)),
+                       ("is_message_present", "u1"), ("pad", "u1", (3,)), ("ldpc_iters", "<i4"),
+                       ("ldpc_nhard", "<i4"), ("message", "u1", (80,))])
+assert ITEM_DTYPE.itemsize == 632
+
+# name -> (generator, flags); flags in the reference CLI's own spelling
+CASES = {
+    "audio_m2_cfg1": dict(gen=lambda: synth.cfg1_demo(seconds=8.0, seed=1)[0], read_mode=1, method=2, center=1500.0,
+                          width=100.0, step=2.0, depth=3, thr=1, llr_blocks=[0, 5], block_dump=[0, 5]),
+    "audio_m2_depth8": dict(gen=lambda: synth.cfg2_deep_audio(seconds=3.0, seed=144, npings=3)[0], read_mode=1, method=2,
+                            center=1500.0, width=60.0, step=1.5, depth=8, thr=4, llr_blocks=[1], block_dump=[1]),
+    "audio_m1_cfg1": dict(gen=lambda: synth.cfg1_demo(seconds=3.0, seed=3)[0], read_mode=1, method=1, center=1500.0,
+                          width=100.0, step=2.0, depth=3, thr=1, llr_blocks=[0], block_dump=[0, 1]),
+    "iq_deep": dict(gen=lambda: synth.cfg3_deep_iq(seconds=1.4, seed=145, npings=2)[0], read_mode=2, method=2, center=0.0,
+                    width=500.0, step=1.0, depth=6, thr=3, llr_blocks=[0], block_dump=[0], llr_subset=800),
+    "audio_deep": dict(gen=lambda: synth.cfg2_deep_audio(seconds=1.4, seed=144, npings=2)[0], read_mode=1, method=2,
+                       center=1500.0, width=500.0, step=1.0, depth=6, thr=3, llr_blocks=[0], block_dump=[0], llr_subset=800),
+}
+
+
+def run_case(name, c, outdir):
+    raw = np.ascontiguousarray(c["gen"]())
+    with tempfile.TemporaryDirectory() as td:
+        inp = os.path.join(td, "in.raw")
+        raw.tofile(inp)
+        prefix = os.path.join(td, "d")
+        subprocess.run([os.path.join(REF, "ref_dump"), "stream", str(c["read_mode"]), str(c["method"]), str(c["center"]),
+                        str(c["width"]), str(c["step"]), str(c["depth"]), str(c["thr"]), inp, prefix], check=True)
+        items = np.fromfile(prefix + ".items.bin", ITEM_DTYPE)
+        blocks = np.fromfile(prefix + ".blocks.c64", np.complex64).reshape(-1, 5184)
+        snr = np.fromfile(prefix + ".snr.i32", np.int32)
+        nb = len(snr)
+        items = items.reshape(nb, -1)
+        cli = [os.path.join(REF, "msk144cudecoder_ref"), f"--search-width={c['width']}", f"--search-step={c['step']}",
+               f"--scan-depth={c['depth']}", f"--nbadsync-threshold={c['thr']}", f"--read-mode={c['read_mode']}",
+               f"--analytic-method={c['method']}", f"--center-frequency={c['center']}"]
+        p = subprocess.run(cli, input=raw.tobytes(), capture_output=True, check=True)
+        lines = [re.sub(r"date=\d{14}", "date=" + "x" * 14, l) for l in p.stdout.decode().splitlines()]
+    present = items["is_message_present"] != 0
+    msg_packed = np.packbits(items["message"][..., :80], axis=-1)  # 10 bytes
+    rng = np.random.default_rng(0)
+    llr_idx, llr_val = [], []
+    for b in c["llr_blocks"]:
+        gated = np.where(items["nbadsync"][b] <= c["thr"])[0]
+        if c.get("llr_subset") and len(gated) > c["llr_subset"]:
+            gated = np.sort(rng.choice(gated, c["llr_subset"], replace=False))
+        llr_idx += [(b, int(i)) for i in gated]
+        llr_val.append(items["llr"][b][gated])
+    out = os.path.join(outdir, name + ".npz")
+    np.savez_compressed(
+        out, read_mode=c["read_mode"], method=c["method"], center=c["center"], width=c["width"], step=c["step"],
+        depth=c["depth"], thr=c["thr"], nblocks=nb, snr=snr,
+        pos=items["pos"].astype(np.uint16), xb=items["xb"], nbadsync=items["nbadsync"].astype(np.int8),
+        present=present, iters=items["ldpc_iters"].astype(np.int8), nhard=items["ldpc_nhard"].astype(np.int8),
+        msg=msg_packed[present], f0=items["f0"][0].reshape(-1, c["depth"], 8)[:, 0, 0],
+        block_dump_idx=np.array(c["block_dump"]), block_dump=blocks[c["block_dump"]],
+        llr_idx=np.array(llr_idx, np.int32).reshape(-1, 2), llr=np.concatenate(llr_val) if llr_val else np.zeros((0, 128), np.float32),
+        cli_lines=np.array(lines))
+    print(f"{name}: {nb} blocks x {items.shape[1]} items, {int(present.sum())} decodes, {len(lines)} cli lines, "
+          f"{os.path.getsize(out) / 1e6:.2f} MB")
+
+
+def run_ldpc(outdir):
+    llrs = []
+    for ebn0 in (0.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0):
+        llrs.append(synth.cfg4_llrs(2500, ebn0, seed=146 + int(ebn0))[0])
+    noise = (np.random.default_rng(9).standard_normal((2000, 128)) * 2).astype(np.float32)
+    llr = np.concatenate(llrs + [noise])
+    with tempfile.TemporaryDirectory() as td:
+        inp, outp = os.path.join(td, "llr.f32"), os.path.join(td, "out.bin")
+        llr.tofile(inp)
+        subprocess.run([os.path.join(REF, "ref_dump"), "ldpc", inp, outp], check=True)
+        rec = np.fromfile(outp, np.dtype([("msg", "u1", (80,)), ("found", "<i4"), ("iters", "<i4"), ("nhard", "<i4")]))
+    assert len(rec) == len(llr)
+    found = rec["found"] != 0
+    out = os.path.join(outdir, "ldpc.npz")
+    np.savez_compressed(out, found=found, iters=rec["iters"].astype(np.int8), nhard=rec["nhard"].astype(np.int8),
+                        msg=np.packbits(rec["msg"][found], axis=-1), llr_sha=np.frombuffer(
+                            __import__("hashlib").sha256(llr.tobytes()).digest(), np.uint8))
+    print(f"ldpc: {len(llr)} codewords, {int(found.sum())} decoded, {os.path.getsize(out) / 1e6:.2f} MB")
+
+
+def golden_ldpc_llrs():
+    llrs = [synth.cfg4_llrs(2500, e, seed=146 + int(e))[0] for e in (0.0, 1.0, 2.0, 3.0, 4.0, 5.0, 6.0, 7.0)]
+    noise = (np.random.default_rng(9).standard_normal((2000, 128)) * 2).astype(np.float32)
+    return np.concatenate(llrs + [noise])
+
+
+if __name__ == "__main__":
+    outdir = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "gpurun_out", "golden")
+    os.makedirs(outdir, exist_ok=True)
+    only = sys.argv[2:]
+    for name, c in CASES.items():
+        if not only or name in only:
+            run_case(name, c, outdir)
+    if not only or "ldpc" in only:
+        run_ldpc(outdir)
