@@ -112,13 +112,17 @@ typedef struct msk144_info {
     int32_t reserved[9];
 } msk144_info;
 
-/* Timing of the last completed launch group, CUDA events on the decoder's stream (milliseconds). */
+/* Per-kernel device time, CUDA events recorded on the launching stream around every kernel of every
+ * launch group since the last msk144_get_stage_times() / decode call (milliseconds, summed). */
 typedef struct msk144_stage_times {
     float frontend_ms, scan_ms, ldpc_ms, total_ms;
     int64_t blocks;        /* blocks in the group */
     int64_t llr_codewords; /* candidates that passed the nbadsync gate */
     int64_t ldpc_successes;
     int64_t kernel_launches; /* kernels launched by this library since creation */
+    int64_t h2d_bytes;       /* host->device bytes copied by the library since creation */
+    int64_t d2h_bytes;       /* device->host bytes copied by the library since creation */
+    int64_t groups;          /* launch groups timed */
 } msk144_stage_times;
 
 typedef struct msk144_decoder msk144_decoder;
@@ -130,7 +134,8 @@ void msk144_config_defaults(msk144_config* cfg); /* code defaults of main.cu:124
 int msk144_create(const msk144_config* cfg, msk144_decoder** out);
 void msk144_destroy(msk144_decoder* dec);
 int msk144_get_info(const msk144_decoder* dec, msk144_info* info);
-int msk144_get_stage_times(const msk144_decoder* dec, msk144_stage_times* t);
+/* Synchronises the stream(s) used since the last call, sums the event pairs, resets the accumulation. */
+int msk144_get_stage_times(msk144_decoder* dec, msk144_stage_times* t);
 
 /* ---- streaming surface: the while(true) loop of main.cu:261-425 ------------------------------------
  * push raw stdin bytes (s16le mono, or s8 I,Q pairs); the library owns the half-block overlap, runs

@@ -58,7 +58,8 @@ class Info(C.Structure):
 class StageTimes(C.Structure):
     _fields_ = [("frontend_ms", C.c_float), ("scan_ms", C.c_float), ("ldpc_ms", C.c_float), ("total_ms", C.c_float),
                 ("blocks", C.c_int64), ("llr_codewords", C.c_int64), ("ldpc_successes", C.c_int64),
-                ("kernel_launches", C.c_int64)]
+                ("kernel_launches", C.c_int64), ("h2d_bytes", C.c_int64), ("d2h_bytes", C.c_int64),
+                ("groups", C.c_int64)]
 
 
 RESULT_DTYPE = np.dtype([("block_index", "<i8"), ("channel", "<i4"), ("item_index", "<u4"), ("freq_idx", "<u4"),

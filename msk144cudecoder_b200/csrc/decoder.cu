@@ -104,7 +104,13 @@ struct msk144_decoder {
     int nf = 0, depth = 0, items = 0, sm_count = 0;
     float if1 = 0.f;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    struct EvQuad {
+        cudaEvent_t e[4];
+        int nb;
+    };
+    std::vector<EvQuad> ev_pool;  // one quad per launch group since the last collect
+    size_t ev_used = 0;
+    int64_t h2d_bytes = 0, d2h_bytes = 0;
 
     // device capacity (blocks per launch group)
     int cap_blocks = 0;
@@ -142,6 +148,8 @@ struct msk144_decoder {
     int ensure_host_results(size_t n);
     int launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
     int fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
+    int next_events(EvQuad** q);
+    void collect_times();
     int decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
                       mskhost::SnrTracker* carry, std::vector<msk144_line>* lines, std::vector<msk144_result>* results);
 };
@@ -156,8 +164,11 @@ void msk144_decoder::release() {
     if (h_powers) cudaFreeHost(h_powers);
     if (h_results) cudaFreeHost(h_results);
     h_counters = nullptr, h_powers = nullptr, h_results = nullptr;
-    for (auto& e : ev)
-        if (e) cudaEventDestroy(e), e = nullptr;
+    for (auto& q : ev_pool)
+        for (auto& e : q.e)
+            if (e) cudaEventDestroy(e), e = nullptr;
+    ev_pool.clear();
+    ev_used = 0;
     if (stream) cudaStreamDestroy(stream), stream = nullptr;
     cap_blocks = 0;
 }
@@ -202,8 +213,37 @@ int msk144_decoder::ensure_host_results(size_t n) {
     return 0;
 }
 
+int msk144_decoder::next_events(EvQuad** q) {
+    if (ev_used == ev_pool.size()) {
+        EvQuad n{};
+        for (auto& e : n.e) CK(cudaEventCreate(&e));
+        ev_pool.push_back(n);
+    }
+    *q = &ev_pool[ev_used++];
+    return 0;
+}
+
+// Sum the event pairs of every launch group recorded since the last collect.  Caller has synchronised.
+void msk144_decoder::collect_times() {
+    for (size_t i = 0; i < ev_used; i++) {
+        EvQuad& q = ev_pool[i];
+        float ms = 0.f;
+        if (cudaEventElapsedTime(&ms, q.e[0], q.e[1]) == cudaSuccess) times.frontend_ms += ms;
+        if (cudaEventElapsedTime(&ms, q.e[1], q.e[2]) == cudaSuccess) times.scan_ms += ms;
+        if (cudaEventElapsedTime(&ms, q.e[2], q.e[3]) == cudaSuccess) times.ldpc_ms += ms;
+        if (cudaEventElapsedTime(&ms, q.e[0], q.e[3]) == cudaSuccess) times.total_ms += ms;
+        times.blocks += q.nb;
+        times.groups += 1;
+    }
+    ev_used = 0;
+}
+
 int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
                                  cudaStream_t st) {
+    EvQuad* evq = nullptr;
+    if (int rc = next_events(&evq)) return rc;
+    cudaEvent_t* ev = evq->e;
+    evq->nb = nb;
     CK(cudaMemsetAsync(d_counters, 0, 4 * sizeof(int), st));
     CK(cudaEventRecord(ev[0], st));
     if (cfg.read_mode == 1 && cfg.analytic_method == 1) {
@@ -274,12 +314,8 @@ int msk144_decoder::fetch_group(int nb, cudaStream_t st, std::vector<RawResult>*
     const int qn = h_counters[0], rn = h_counters[1];
     if (static_cast<size_t>(qn) > queue_cap || static_cast<size_t>(rn) > result_cap)
         return fail(MSK144_EOVERFLOW, "device queue overflow");
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev[0], ev[1]), times.frontend_ms += ms;
-    cudaEventElapsedTime(&ms, ev[1], ev[2]), times.scan_ms += ms;
-    cudaEventElapsedTime(&ms, ev[2], ev[3]), times.ldpc_ms += ms;
-    cudaEventElapsedTime(&ms, ev[0], ev[3]), times.total_ms += ms;
-    times.blocks += nb;
+    collect_times();
+    d2h_bytes += 4 * sizeof(int) + static_cast<size_t>(nb) * 8 * sizeof(float);
     times.llr_codewords += qn;
     times.ldpc_successes += rn;
     if (powers) powers->insert(powers->end(), h_powers, h_powers + static_cast<size_t>(nb) * 8);
@@ -287,6 +323,7 @@ int msk144_decoder::fetch_group(int nb, cudaStream_t st, std::vector<RawResult>*
         if (int rc = ensure_host_results(rn)) return rc;
         CK(cudaMemcpyAsync(h_results, d_results, static_cast<size_t>(rn) * sizeof(ResultRec), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
+        d2h_bytes += static_cast<size_t>(rn) * sizeof(ResultRec);
         if (out)
             for (int i = 0; i < rn; i++) out->push_back(RawResult{gblock0 + h_results[i].block, h_results[i]});
     }
@@ -297,6 +334,7 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
                                   mskhost::SnrTracker* carry, std::vector<msk144_line>* lines,
                                   std::vector<msk144_result>* results) {
     times = msk144_stage_times{};
+    ev_used = 0;
     const int64_t bpc = spc >= static_cast<size_t>(N) ? static_cast<int64_t>((spc - N) / (N / 2)) + 1 : 0;
     const int64_t total = bpc * nchan;
     if (total == 0) return 0;
@@ -440,7 +478,6 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
         if (e_ != cudaSuccess) return bail(fail(MSK144_ECUDA, std::string(#call) + ": " + cudaGetErrorString(e_))); \
     } while (0)
     CKD(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
-    for (auto& e : d->ev) CKD(cudaEventCreate(&e));
     DevTables tab;
     build_tables(&tab);
     CKD(cudaMemcpyToSymbol(c_tab, &tab, sizeof(tab)));
@@ -495,10 +532,18 @@ int msk144_get_info(const msk144_decoder* dec, msk144_info* info) {
     return MSK144_OK;
 }
 
-int msk144_get_stage_times(const msk144_decoder* dec, msk144_stage_times* t) {
+int msk144_get_stage_times(msk144_decoder* dec, msk144_stage_times* t) {
     if (!dec || !t) return fail(MSK144_EINVAL, "null argument");
+    if (dec->ev_used > 0) {  // groups launched by msk144_run_device and not yet timed
+        CK(cudaSetDevice(dec->cfg.device));
+        CK(cudaDeviceSynchronize());
+        dec->collect_times();
+    }
     *t = dec->times;
     t->kernel_launches = dec->launches;
+    t->h2d_bytes = dec->h2d_bytes;
+    t->d2h_bytes = dec->d2h_bytes;
+    dec->times = msk144_stage_times{};
     return MSK144_OK;
 }
 
@@ -535,6 +580,7 @@ int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int
     const size_t bytes = spc * static_cast<size_t>(nchan) * 2;  // s16 mono or s8 I + s8 Q: 2 bytes per sample
     if (int rc = dec->ensure_raw(bytes)) return rc;
     CK(cudaMemcpyAsync(dec->d_raw, samples, bytes, cudaMemcpyHostToDevice, dec->stream));
+    dec->h2d_bytes += bytes;
     return msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results, result_cap,
                                 nresults);
 }
@@ -578,6 +624,7 @@ int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
     const size_t used_samples = (nblocks - 1) * (N / 2) + N;
     if (int rc = dec->ensure_raw(used_samples * 2)) return rc;
     CK(cudaMemcpyAsync(dec->d_raw, dec->pending.data(), used_samples * 2, cudaMemcpyHostToDevice, dec->stream));
+    dec->h2d_bytes += used_samples * 2;
     std::vector<msk144_line> lv;
     if (int rc = dec->decode_common(dec->d_raw, used_samples, 1, dec->stream, dec->next_block, &dec->stream_snr, &lv,
                                     nullptr))
