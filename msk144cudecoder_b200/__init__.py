@@ -170,15 +170,17 @@ class Decoder:
         lines = (Line * line_cap)()
         results = np.zeros(result_cap, RESULT_DTYPE)
         nl, nr = C.c_size_t(0), C.c_size_t(0)
-        rc = fn(self._h, ptr, spc, nchan, *extra, lines, line_cap, C.byref(nl), results.ctypes.data, result_cap,
-                C.byref(nr))
+        rc = fn(self._h, ptr, spc, nchan, *extra, lines, line_cap, C.byref(nl),
+                results.ctypes.data if result_cap else None, result_cap, C.byref(nr) if result_cap else None)
         if rc == -5 and (nl.value > line_cap or nr.value > result_cap):  # grow and retry once
-            return self._decode(fn, ptr, spc, nchan, extra, max(line_cap, nl.value), max(result_cap, nr.value))
+            return self._decode(fn, ptr, spc, nchan, extra, max(line_cap, nl.value),
+                                max(result_cap, nr.value) if result_cap else 0)
         _check(rc)
         return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
 
     def decode_host(self, samples: np.ndarray, nchan: int = 1, line_cap: int = 4096, result_cap: int = 1 << 16):
-        """samples: int16 (audio) or int8 I,Q pairs, `nchan` equal-length channels back to back."""
+        """samples: int16 (audio) or int8 I,Q pairs, `nchan` equal-length channels back to back.
+        result_cap = 0: decode lines only (the per-candidate LDPC successes are not returned)."""
         samples = np.ascontiguousarray(samples)
         spc = samples.nbytes // 2 // nchan
         return self._decode(lib().msk144_decode_host, samples.ctypes.data, spc, nchan, (), line_cap, result_cap)

@@ -125,6 +125,7 @@ struct msk144_decoder {
     size_t d_raw_bytes = 0;
     float2* d_twiddle = nullptr;
     float* d_hfilt = nullptr;
+    unsigned short* d_edge_tab = nullptr;
 
     int* h_counters = nullptr;  // pinned
     float* h_powers = nullptr;  // pinned [cap][8]
@@ -157,7 +158,8 @@ struct msk144_decoder {
 void msk144_decoder::release() {
     cudaSetDevice(cfg.device);
     cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
-    cudaFree(d_counters), cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt);
+    cudaFree(d_counters), cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt), cudaFree(d_edge_tab);
+    d_edge_tab = nullptr;
     d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
     d_counters = nullptr, d_raw = nullptr, d_twiddle = nullptr, d_hfilt = nullptr;
     if (h_counters) cudaFreeHost(h_counters);
@@ -299,6 +301,7 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
     lp.result_count = d_counters + 1;
     lp.result_cap = static_cast<int>(std::min<size_t>(result_cap, 0x7fffffffull));
     lp.flat_out = nullptr;
+    lp.edge_tab = d_edge_tab;
     ldpc_kernel<<<sm_count * 8, LDPC_WARPS * 32, 0, st>>>(lp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[3], st));
@@ -481,6 +484,8 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
     DevTables tab;
     build_tables(&tab);
     CKD(cudaMemcpyToSymbol(c_tab, &tab, sizeof(tab)));
+    CKD(cudaMalloc(&d->d_edge_tab, sizeof(tab.edge)));
+    CKD(cudaMemcpy(d->d_edge_tab, tab.edge, sizeof(tab.edge), cudaMemcpyHostToDevice));
     CKD(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
     CKD(cudaFuncSetAttribute(fft_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FFT_SMEM)));
     CKD(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
@@ -772,6 +777,7 @@ int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t nc
     lp.count = static_cast<int>(ncw);
     lp.cap = static_cast<int>(ncw);
     lp.flat_out = reinterpret_cast<uint4*>(d_out);
+    lp.edge_tab = dec->d_edge_tab;
     const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * 8, (ncw + LDPC_WARPS - 1) / LDPC_WARPS));
     if (grid > 0) {
         ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);

@@ -13,6 +13,18 @@ for step in "$@"; do
     golden) timeout 900 python tools/make_golden.py gpurun_out/golden > gpurun_out/golden.log 2>&1; echo "golden rc=$?"; tail -12 gpurun_out/golden.log ;;
     bench)  timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.log; tail -5 gpurun_out/bench.err ;;
     benchref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2> gpurun_out/bench_ref.err; echo "benchref rc=$?"; tail -3 gpurun_out/bench_ref.log; tail -5 gpurun_out/bench_ref.err ;;
+    stages) timeout 600 python tools/bench_stages.py > gpurun_out/stages.log 2>&1; echo "stages rc=$?"; cat gpurun_out/stages.log | cut -c1-400 ;;
+    quick)  timeout 900 python -m pytest tests/test_golden.py tests/test_gpu_parity.py -m gpu -q -x --timeout=600 -k "ldpc or cli or stream_lines" > gpurun_out/pytest_quick.log 2>&1; echo "quick rc=$?"; tail -5 gpurun_out/pytest_quick.log ;;
+    ncu_list)
+      CMD="python bench.py --steps 1 --warmup 1 --seconds 60 --no-cpu-baseline"
+      $CMD > gpurun_out/ncu_plain.log 2>&1 &&
+      ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_list.log 2>&1
+      echo "ncu_list rc=$?"; tail -2 gpurun_out/ncu_plain.log; wc -l gpurun_out/launches.csv ;;
+    ncu_full)
+      CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
+      $CMD > gpurun_out/ncu_plain2.log 2>&1 &&
+      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 3 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
+      echo "ncu_full rc=$?"; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/*.ncu-rep ;;
     *) echo "unknown step $step" ;;
   esac
 done
