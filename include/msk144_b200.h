@@ -181,6 +181,11 @@ int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, u
  * {bits 0..31, 32..63, 64..76 | found<<31, iters | nhard<<8}. */
 int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t ncw, uint32_t* d_out, void* stream);
 
+/* Device self-test of the LDPC kernel's packed math: all 2^32 float inputs through the f32x2 tanh and the
+ * division-free platanh against libdevice tanhf and the reference's platanh (ldpc_kernel.cuh:65-93) with an
+ * IEEE division.  Counts of mismatching inputs; both must be 0 for bit-exact LDPC parity. */
+int msk144_selftest_ldpc_math(msk144_decoder* dec, uint64_t* tanh_mismatches, uint64_t* platanh_mismatches);
+
 /* ---- host post-processing, exported for the CLI and for callers that bring their own GPU stage ---- */
 /* decode_softbits.cpp:23-55 (i3/n3 gate + unpack77 + right trim). 1 = found. text: >= 38 bytes. */
 int msk144_decode_message(const uint8_t* msg77, char* text);

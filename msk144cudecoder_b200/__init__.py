@@ -107,6 +107,7 @@ def lib():
         L.msk144_scan_host.argtypes = [vp, vp, C.c_int64, vp, vp, vp, sz, C.POINTER(sz)]
         L.msk144_ldpc_decode_host.argtypes = [vp, vp, sz, vp, vp, vp, vp]
         L.msk144_ldpc_decode_device.argtypes = [vp, vp, sz, vp, vp]
+        L.msk144_selftest_ldpc_math.argtypes = [vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.msk144_decode_message.argtypes = [vp, C.c_char_p]
         L.msk144_format_line.argtypes = [C.POINTER(Line), C.c_char_p, C.c_char_p, sz]
         L.msk144_unpack77_reset.argtypes = []
@@ -248,6 +249,13 @@ class Decoder:
         _check(lib().msk144_ldpc_decode_host(self._h, llr.ctypes.data, n, found.ctypes.data, msg.ctypes.data,
                                              iters.ctypes.data, nhard.ctypes.data))
         return found.astype(bool), msg, iters, nhard
+
+    def selftest_ldpc_math(self) -> Tuple[int, int]:
+        """All 2^32 floats through the LDPC kernel's packed tanh / platanh vs their scalar definitions:
+        (tanh mismatches, platanh mismatches)."""
+        a, b = C.c_uint64(0), C.c_uint64(0)
+        _check(lib().msk144_selftest_ldpc_math(self._h, C.byref(a), C.byref(b)))
+        return int(a.value), int(b.value)
 
     def ldpc_decode_device(self, d_llr: int, ncw: int, d_out: int, stream: int = 0):
         _check(lib().msk144_ldpc_decode_device(self._h, d_llr, ncw, d_out, C.c_void_p(stream)))

@@ -151,6 +151,15 @@ struct msk144_decoder {
     int fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
     int next_events(EvQuad** q);
     void collect_times();
+    void fill_ldpc_tables(LdpcParams* lp) const {
+        lp->edge_tab = d_edge_tab;
+        // platanh segment constants (ldpc_kernel.cuh:75-90) and their correctly rounded reciprocals
+        const float c[4] = {0.0f, 0.4064f, 0.8378f, 0.9914f}, dv[4] = {0.83f, 0.322f, 0.0524f, 0.0012f};
+        for (int k = 0; k < 4; k++) {
+            volatile float r = 1.0f / dv[k];  // IEEE single division, as the exhaustive division proof assumes
+            lp->pc[k] = c[k], lp->pd[k] = dv[k], lp->pr[k] = r;
+        }
+    }
     int decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
                       mskhost::SnrTracker* carry, std::vector<msk144_line>* lines, std::vector<msk144_result>* results);
 };
@@ -301,8 +310,8 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
     lp.result_count = d_counters + 1;
     lp.result_cap = static_cast<int>(std::min<size_t>(result_cap, 0x7fffffffull));
     lp.flat_out = nullptr;
-    lp.edge_tab = d_edge_tab;
-    ldpc_kernel<<<sm_count * 8, LDPC_WARPS * 32, 0, st>>>(lp);
+    fill_ldpc_tables(&lp);
+    ldpc_kernel<<<sm_count * 2, LDPC_WARPS * 32, 0, st>>>(lp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[3], st));
     launches += 3;
@@ -777,8 +786,9 @@ int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t nc
     lp.count = static_cast<int>(ncw);
     lp.cap = static_cast<int>(ncw);
     lp.flat_out = reinterpret_cast<uint4*>(d_out);
-    lp.edge_tab = dec->d_edge_tab;
-    const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * 8, (ncw + LDPC_WARPS - 1) / LDPC_WARPS));
+    dec->fill_ldpc_tables(&lp);
+    const size_t npairs = (ncw + 1) / 2;
+    const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * 2, (npairs + LDPC_WARPS - 1) / LDPC_WARPS));
     if (grid > 0) {
         ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
         CK(cudaGetLastError());
@@ -829,6 +839,27 @@ int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, u
             nhard[i] = (nh == 0xff) ? -1 : nh;
         }
     }
+    return MSK144_OK;
+}
+
+int msk144_selftest_ldpc_math(msk144_decoder* dec, uint64_t* tanh_mismatches, uint64_t* platanh_mismatches) {
+    if (!dec) return fail(MSK144_EINVAL, "null argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    unsigned long long* d_m = nullptr;
+    CK(cudaMalloc(&d_m, 2 * sizeof(unsigned long long)));
+    cudaMemsetAsync(d_m, 0, 2 * sizeof(unsigned long long), dec->stream);
+    LdpcParams lp{};
+    dec->fill_ldpc_tables(&lp);
+    ldpc_math_selftest_kernel<<<dec->sm_count * 8, 256, 0, dec->stream>>>(lp, d_m);
+    unsigned long long h[2] = {~0ull, ~0ull};
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_m, sizeof(h), cudaMemcpyDeviceToHost, dec->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(dec->stream);
+    cudaFree(d_m);
+    if (e != cudaSuccess) return fail(MSK144_ECUDA, std::string("selftest: ") + cudaGetErrorString(e));
+    dec->launches += 1;
+    if (tanh_mismatches) *tanh_mismatches = h[0];
+    if (platanh_mismatches) *platanh_mismatches = h[1];
     return MSK144_OK;
 }
 
