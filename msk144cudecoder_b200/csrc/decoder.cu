@@ -126,6 +126,7 @@ struct msk144_decoder {
     float2* d_twiddle = nullptr;
     float* d_hfilt = nullptr;
     unsigned short* d_edge_tab = nullptr;
+    float2* d_mix = nullptr;  // [nf][N] mixer table e^{j phi(f, i)}
 
     int* h_counters = nullptr;  // pinned
     float* h_powers = nullptr;  // pinned [cap][8]
@@ -168,7 +169,8 @@ void msk144_decoder::release() {
     cudaSetDevice(cfg.device);
     cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
     cudaFree(d_counters), cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt), cudaFree(d_edge_tab);
-    d_edge_tab = nullptr;
+    cudaFree(d_mix);
+    d_edge_tab = nullptr, d_mix = nullptr;
     d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
     d_counters = nullptr, d_raw = nullptr, d_twiddle = nullptr, d_hfilt = nullptr;
     if (h_counters) cudaFreeHost(h_counters);
@@ -283,6 +285,7 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
     CK(cudaEventRecord(ev[1], st));
     ScanParams sp;
     sp.blocks = d_blocks;
+    sp.mix = d_mix;
     sp.nf = nf;
     sp.depth = depth;
     sp.thr = cfg.nbadsync_threshold;
@@ -498,6 +501,23 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
     CKD(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
     CKD(cudaFuncSetAttribute(fft_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FFT_SMEM)));
     CKD(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
+    {
+        // mixer table, once per decoder (scan_kernel.cuh:45-69 evaluates it per block and frequency)
+        const size_t bytes = static_cast<size_t>(d->nf) * N * sizeof(float2);
+        if (bytes > (64ull << 30)) return bail(fail(MSK144_EINVAL, "frequency grid too large for the mixer table"));
+        CKD(cudaMalloc(&d->d_mix, bytes));
+        MixParams mp;
+        mp.table = d->d_mix;
+        mp.nf = d->nf;
+        mp.center = cfg->center_frequency_hz;
+        mp.if1 = d->if1;
+        mp.step = cfg->search_step_hz;
+        if (d->nf > 65535) return bail(fail(MSK144_EINVAL, "more than 65535 search frequencies"));
+        mix_table_kernel<<<dim3((N + 255) / 256, d->nf), 256, 0, d->stream>>>(mp);
+        CKD(cudaGetLastError());
+        CKD(cudaStreamSynchronize(d->stream));
+        d->launches += 1;
+    }
     CKD(cudaMalloc(&d->d_counters, 4 * sizeof(int)));
     CKD(cudaMallocHost(&d->h_counters, 4 * sizeof(int)));
     if (cfg->read_mode == 1 && cfg->analytic_method == 1) {
@@ -727,6 +747,7 @@ int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nbl
         CK(cudaMemsetAsync(dec->d_counters, 0, 4 * sizeof(int), dec->stream));
         ScanParams sp;
         sp.blocks = dec->d_blocks;
+        sp.mix = dec->d_mix;
         sp.nf = dec->nf;
         sp.depth = dec->depth;
         sp.thr = dec->cfg.nbadsync_threshold;
