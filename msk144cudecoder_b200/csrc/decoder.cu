@@ -92,6 +92,17 @@ void build_tables(DevTables* t) {
     }
 }
 
+// scan_kernel is instantiated per scan depth (msk_context.cuh:28-33 clamps it to 1..8)
+using ScanEntry = void (*)(ScanParams);
+ScanEntry scan_entry(int depth) {
+    static const ScanEntry tab[8] = {scan_kernel<1>, scan_kernel<2>, scan_kernel<3>, scan_kernel<4>,
+                                     scan_kernel<5>, scan_kernel<6>, scan_kernel<7>, scan_kernel<8>};
+    return tab[std::max(1, std::min(8, depth)) - 1];
+}
+void launch_scan(int depth, dim3 grid, cudaStream_t st, const ScanParams& sp) {
+    scan_entry(depth)<<<grid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
+}
+
 struct RawResult {
     int64_t gblock;
     ResultRec r;
@@ -299,7 +310,7 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
     sp.queue_count = d_counters;
     sp.queue_cap = static_cast<int>(std::min<size_t>(queue_cap, static_cast<size_t>(nb) * items));
     dim3 sgrid((nf + sp.fpc - 1) / sp.fpc, nb);
-    scan_kernel<<<sgrid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
+    launch_scan(depth, sgrid, st, sp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[2], st));
     LdpcParams lp{};
@@ -500,7 +511,7 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
     CKD(cudaMemcpy(d->d_edge_tab, tab.edge, sizeof(tab.edge), cudaMemcpyHostToDevice));
     CKD(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
     CKD(cudaFuncSetAttribute(fft_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FFT_SMEM)));
-    CKD(cudaFuncSetAttribute(scan_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
+    CKD(cudaFuncSetAttribute(scan_entry(d->depth), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
     {
         // mixer table, once per decoder (scan_kernel.cuh:45-69 evaluates it per block and frequency)
         const size_t bytes = static_cast<size_t>(d->nf) * N * sizeof(float2);
@@ -761,7 +772,7 @@ int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nbl
         sp.queue_count = dec->d_counters;
         sp.queue_cap = static_cast<int>(static_cast<size_t>(nb) * dec->items);
         dim3 sgrid((dec->nf + sp.fpc - 1) / sp.fpc, nb);
-        scan_kernel<<<sgrid, SCAN_THREADS, SCAN_SMEM, dec->stream>>>(sp);
+        launch_scan(dec->depth, sgrid, dec->stream, sp);
         CK(cudaGetLastError());
         dec->launches += 1;
         CK(cudaMemcpyAsync(dec->h_counters, dec->d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, dec->stream));
