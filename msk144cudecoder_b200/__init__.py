@@ -18,7 +18,7 @@ from typing import List, Optional, Tuple
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libmsk144b200.so")
+LIB_PATH = os.environ.get("MSK144_B200_LIB") or os.path.join(_HERE, "lib", "libmsk144b200.so")  # override: A/B builds
 CLI_PATH = os.path.join(_HERE, "bin", "msk144cudecoder")
 
 BLOCK_SAMPLES, HOP_SAMPLES = 5184, 2592

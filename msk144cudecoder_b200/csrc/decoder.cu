@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <deque>
 #include <string>
@@ -123,15 +124,23 @@ struct msk144_decoder {
     size_t ev_used = 0;
     int64_t h2d_bytes = 0, d2h_bytes = 0;
 
-    // device capacity (blocks per launch group)
-    int cap_blocks = 0;
-    float2* d_blocks = nullptr;
-    float* d_powers = nullptr;
-    CandRec* d_cands = nullptr;
-    QueueRec* d_queue = nullptr;
-    ResultRec* d_results = nullptr;
-    int* d_counters = nullptr;  // [0] queue count, [1] result count
+    // Device buffers of one launch group.  Two slots: while the host fetches and unpacks group g, the
+    // kernels of group g+1 already run (copies go through copy_stream, ordered by the slot's event).
+    struct Slot {
+        float2* d_blocks = nullptr;
+        float* d_powers = nullptr;
+        CandRec* d_cands = nullptr;
+        QueueRec* d_queue = nullptr;
+        ResultRec* d_results = nullptr;
+        int* d_counters = nullptr;  // [0] queue count, [1] result count
+        int* h_counters = nullptr;  // pinned
+        float* h_powers = nullptr;  // pinned [cap][8]
+        cudaEvent_t done = nullptr; // recorded on the launching stream after the slot's last kernel
+    };
+    Slot slot[2];
+    int cap_blocks = 0;  // device capacity (blocks per launch group)
     size_t queue_cap = 0, result_cap = 0;
+    cudaStream_t copy_stream = nullptr;
     void* d_raw = nullptr;
     size_t d_raw_bytes = 0;
     float2* d_twiddle = nullptr;
@@ -139,9 +148,7 @@ struct msk144_decoder {
     unsigned short* d_edge_tab = nullptr;
     float2* d_mix = nullptr;  // [nf][N] mixer table e^{j phi(f, i)}
 
-    int* h_counters = nullptr;  // pinned
-    float* h_powers = nullptr;  // pinned [cap][8]
-    ResultRec* h_results = nullptr;
+    ResultRec* h_results = nullptr;  // pinned
     size_t h_results_cap = 0;
 
     // accumulated by the last decode call
@@ -159,10 +166,17 @@ struct msk144_decoder {
     int ensure_capacity(int nblocks);
     int ensure_raw(size_t bytes);
     int ensure_host_results(size_t n);
-    int launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
-    int fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
+    int launch_group(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
+    int fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
     int next_events(EvQuad** q);
     void collect_times();
+    // frequencies walked by one scan CTA: enough to amortise the pipeline prologue, few enough that the grid
+    // still holds several waves of CTAs per SM
+    int scan_fpc(int nb) const {
+        int cap = 8;
+        if (const char* e = std::getenv("MSK144_SCAN_FPC")) cap = std::max(1, std::atoi(e));  // tuning knob
+        return std::max(1, std::min(cap, static_cast<int>((static_cast<long long>(nf) * nb) / (sm_count * 8))));
+    }
     void fill_ldpc_tables(LdpcParams* lp) const {
         lp->edge_tab = d_edge_tab;
         // platanh segment constants (ldpc_kernel.cuh:75-90) and their correctly rounded reciprocals
@@ -178,41 +192,47 @@ struct msk144_decoder {
 
 void msk144_decoder::release() {
     cudaSetDevice(cfg.device);
-    cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
-    cudaFree(d_counters), cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt), cudaFree(d_edge_tab);
-    cudaFree(d_mix);
-    d_edge_tab = nullptr, d_mix = nullptr;
-    d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
-    d_counters = nullptr, d_raw = nullptr, d_twiddle = nullptr, d_hfilt = nullptr;
-    if (h_counters) cudaFreeHost(h_counters);
-    if (h_powers) cudaFreeHost(h_powers);
+    for (Slot& sl : slot) {
+        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
+        cudaFree(sl.d_counters);
+        if (sl.h_counters) cudaFreeHost(sl.h_counters);
+        if (sl.h_powers) cudaFreeHost(sl.h_powers);
+        if (sl.done) cudaEventDestroy(sl.done);
+        sl = Slot{};
+    }
+    cudaFree(d_raw), cudaFree(d_twiddle), cudaFree(d_hfilt), cudaFree(d_edge_tab), cudaFree(d_mix);
+    d_edge_tab = nullptr, d_mix = nullptr, d_raw = nullptr, d_twiddle = nullptr, d_hfilt = nullptr;
     if (h_results) cudaFreeHost(h_results);
-    h_counters = nullptr, h_powers = nullptr, h_results = nullptr;
+    h_results = nullptr;
     for (auto& q : ev_pool)
         for (auto& e : q.e)
             if (e) cudaEventDestroy(e), e = nullptr;
     ev_pool.clear();
     ev_used = 0;
     if (stream) cudaStreamDestroy(stream), stream = nullptr;
+    if (copy_stream) cudaStreamDestroy(copy_stream), copy_stream = nullptr;
     cap_blocks = 0;
 }
 
 int msk144_decoder::ensure_capacity(int nblocks) {
     if (nblocks <= cap_blocks) return 0;
-    cudaFree(d_blocks), cudaFree(d_powers), cudaFree(d_cands), cudaFree(d_queue), cudaFree(d_results);
-    d_blocks = nullptr, d_powers = nullptr, d_cands = nullptr, d_queue = nullptr, d_results = nullptr;
-    if (h_powers) cudaFreeHost(h_powers), h_powers = nullptr;
+    CK(cudaDeviceSynchronize());
     cap_blocks = 0;
     const size_t nb = static_cast<size_t>(nblocks);
     queue_cap = nb * items;  // worst case: every candidate passes the sync gate
     result_cap = nb * items;
     if (queue_cap > 0x7fffffffull) return fail(MSK144_EINVAL, "batch too large");
-    CK(cudaMalloc(&d_blocks, nb * N * sizeof(float2)));
-    CK(cudaMalloc(&d_powers, nb * 8 * sizeof(float)));
-    CK(cudaMalloc(&d_cands, nb * items * sizeof(CandRec)));
-    CK(cudaMalloc(&d_queue, queue_cap * sizeof(QueueRec)));
-    CK(cudaMalloc(&d_results, result_cap * sizeof(ResultRec)));
-    CK(cudaMallocHost(&h_powers, nb * 8 * sizeof(float)));
+    for (Slot& sl : slot) {
+        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
+        sl.d_blocks = nullptr, sl.d_powers = nullptr, sl.d_cands = nullptr, sl.d_queue = nullptr, sl.d_results = nullptr;
+        if (sl.h_powers) cudaFreeHost(sl.h_powers), sl.h_powers = nullptr;
+        CK(cudaMalloc(&sl.d_blocks, nb * N * sizeof(float2)));
+        CK(cudaMalloc(&sl.d_powers, nb * 8 * sizeof(float)));
+        CK(cudaMalloc(&sl.d_cands, nb * items * sizeof(CandRec)));
+        CK(cudaMalloc(&sl.d_queue, queue_cap * sizeof(QueueRec)));
+        CK(cudaMalloc(&sl.d_results, result_cap * sizeof(ResultRec)));
+        CK(cudaMallocHost(&sl.h_powers, nb * 8 * sizeof(float)));
+    }
     cap_blocks = nblocks;
     return 0;
 }
@@ -262,13 +282,13 @@ void msk144_decoder::collect_times() {
     ev_used = 0;
 }
 
-int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
+int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
                                  cudaStream_t st) {
     EvQuad* evq = nullptr;
     if (int rc = next_events(&evq)) return rc;
     cudaEvent_t* ev = evq->e;
     evq->nb = nb;
-    CK(cudaMemsetAsync(d_counters, 0, 4 * sizeof(int), st));
+    CK(cudaMemsetAsync(sl.d_counters, 0, 4 * sizeof(int), st));
     CK(cudaEventRecord(ev[0], st));
     if (cfg.read_mode == 1 && cfg.analytic_method == 1) {
         FftParams fp;
@@ -278,8 +298,8 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
         fp.block0 = block0;
         fp.twiddle = d_twiddle;
         fp.hfilt = d_hfilt;
-        fp.out = d_blocks;
-        fp.powers = d_powers;
+        fp.out = sl.d_blocks;
+        fp.powers = sl.d_powers;
         fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, st>>>(fp);
     } else {
         FrontParams fp;
@@ -288,67 +308,69 @@ int msk144_decoder::launch_group(const void* d_in, long long chan_stride, int bp
         fp.bpc = bpc;
         fp.read_mode = cfg.read_mode;
         fp.block0 = block0;
-        fp.out = d_blocks;
-        fp.powers = d_powers;
+        fp.out = sl.d_blocks;
+        fp.powers = sl.d_powers;
         frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, st>>>(fp);
     }
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[1], st));
     ScanParams sp;
-    sp.blocks = d_blocks;
+    sp.blocks = sl.d_blocks;
     sp.mix = d_mix;
     sp.nf = nf;
     sp.depth = depth;
     sp.thr = cfg.nbadsync_threshold;
-    sp.fpc = std::max(1, std::min(8, static_cast<int>((static_cast<long long>(nf) * nb) / (sm_count * 8))));
+    sp.fpc = scan_fpc(nb);
     sp.center = cfg.center_frequency_hz;
     sp.if1 = if1;
     sp.step = cfg.search_step_hz;
     sp.block0 = 0;
-    sp.cands = d_cands;
-    sp.queue = d_queue;
-    sp.queue_count = d_counters;
+    sp.cands = sl.d_cands;
+    sp.queue = sl.d_queue;
+    sp.queue_count = sl.d_counters;
     sp.queue_cap = static_cast<int>(std::min<size_t>(queue_cap, static_cast<size_t>(nb) * items));
     dim3 sgrid((nf + sp.fpc - 1) / sp.fpc, nb);
     launch_scan(depth, sgrid, st, sp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[2], st));
     LdpcParams lp{};
-    lp.llr = reinterpret_cast<const float*>(d_queue) + 8;
+    lp.llr = reinterpret_cast<const float*>(sl.d_queue) + 8;
     lp.stride = sizeof(QueueRec) / sizeof(float);
-    lp.count_ptr = d_counters;
+    lp.count_ptr = sl.d_counters;
     lp.count = 0;
     lp.cap = sp.queue_cap;
-    lp.queue = d_queue;
-    lp.results = d_results;
-    lp.result_count = d_counters + 1;
+    lp.queue = sl.d_queue;
+    lp.results = sl.d_results;
+    lp.result_count = sl.d_counters + 1;
     lp.result_cap = static_cast<int>(std::min<size_t>(result_cap, 0x7fffffffull));
     lp.flat_out = nullptr;
     fill_ldpc_tables(&lp);
-    ldpc_kernel<<<sm_count * 2, LDPC_WARPS * 32, 0, st>>>(lp);
+    ldpc_kernel<<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[3], st));
+    CK(cudaEventRecord(sl.done, st));
     launches += 3;
     return 0;
 }
 
-int msk144_decoder::fetch_group(int nb, cudaStream_t st, std::vector<RawResult>* out, int64_t gblock0,
+int msk144_decoder::fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, int64_t gblock0,
                                 std::vector<float>* powers) {
-    CK(cudaMemcpyAsync(h_counters, d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(h_powers, d_powers, static_cast<size_t>(nb) * 8 * sizeof(float), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    const int qn = h_counters[0], rn = h_counters[1];
+    cudaStream_t cs = copy_stream;
+    CK(cudaStreamWaitEvent(cs, sl.done, 0));
+    CK(cudaMemcpyAsync(sl.h_counters, sl.d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, cs));
+    CK(cudaMemcpyAsync(sl.h_powers, sl.d_powers, static_cast<size_t>(nb) * 8 * sizeof(float), cudaMemcpyDeviceToHost, cs));
+    CK(cudaStreamSynchronize(cs));
+    const int qn = sl.h_counters[0], rn = sl.h_counters[1];
     if (static_cast<size_t>(qn) > queue_cap || static_cast<size_t>(rn) > result_cap)
         return fail(MSK144_EOVERFLOW, "device queue overflow");
-    collect_times();
     d2h_bytes += 4 * sizeof(int) + static_cast<size_t>(nb) * 8 * sizeof(float);
     times.llr_codewords += qn;
     times.ldpc_successes += rn;
-    if (powers) powers->insert(powers->end(), h_powers, h_powers + static_cast<size_t>(nb) * 8);
+    if (powers) powers->insert(powers->end(), sl.h_powers, sl.h_powers + static_cast<size_t>(nb) * 8);
     if (rn > 0) {
         if (int rc = ensure_host_results(rn)) return rc;
-        CK(cudaMemcpyAsync(h_results, d_results, static_cast<size_t>(rn) * sizeof(ResultRec), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
+        CK(cudaMemcpyAsync(h_results, sl.d_results, static_cast<size_t>(rn) * sizeof(ResultRec), cudaMemcpyDeviceToHost, cs));
+        CK(cudaStreamSynchronize(cs));
         d2h_bytes += static_cast<size_t>(rn) * sizeof(ResultRec);
         if (out)
             for (int i = 0; i < rn; i++) out->push_back(RawResult{gblock0 + h_results[i].block, h_results[i]});
@@ -369,26 +391,22 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
     if (int rc = ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
     std::vector<RawResult> raw;
     std::vector<float> powers;
-    powers.reserve(static_cast<size_t>(total) * 8);
-    for (int64_t g0 = 0; g0 < total; g0 += group) {
-        const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
-        if (int rc = launch_group(d_in, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
-        if (int rc = fetch_group(nb, st, &raw, g0, &powers)) return rc;
-    }
-    times.kernel_launches = launches;
-    // ---- host post-processing, block by block in stream order (main.cu:388-419) ----
-    std::sort(raw.begin(), raw.end(), [](const RawResult& a, const RawResult& b) {
-        if (a.gblock != b.gblock) return a.gblock < b.gblock;
-        return a.r.item < b.r.item;
-    });
     const bool compat = (cfg.flags & MSK144_FLAG_COMPAT_DECODE_CACHE) != 0;
-    size_t ri = 0;
-    for (int ch = 0; ch < nchan; ch++) {
-        mskhost::SnrTracker local;
-        mskhost::SnrTracker* snr = (carry && nchan == 1) ? carry : &local;
-        for (int64_t k = 0; k < bpc; k++) {
-            const int64_t gb = static_cast<int64_t>(ch) * bpc + k;
-            snr->process_powers(&powers[static_cast<size_t>(gb) * 8]);
+    mskhost::SnrTracker local;
+    // host post-processing of one fetched group, block by block in stream order (main.cu:388-419); it runs
+    // while the GPU works on the next group
+    auto process = [&](int64_t g0, int nb) {
+        std::sort(raw.begin(), raw.end(), [](const RawResult& a, const RawResult& b) {
+            if (a.gblock != b.gblock) return a.gblock < b.gblock;
+            return a.r.item < b.r.item;
+        });
+        size_t ri = 0;
+        for (int64_t gb = g0; gb < g0 + nb; gb++) {
+            const int ch = static_cast<int>(gb / bpc);
+            const int64_t k = gb % bpc;
+            if (k == 0) local = mskhost::SnrTracker();  // every channel starts a fresh SNR recurrence
+            mskhost::SnrTracker* snr = (carry && nchan == 1) ? carry : &local;
+            snr->process_powers(&powers[static_cast<size_t>(gb - g0) * 8]);
             std::vector<mskhost::Present> present;
             while (ri < raw.size() && raw[ri].gblock == gb) {
                 const ResultRec& r = raw[ri].r;
@@ -396,11 +414,8 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
                 p.item = r.item;
                 p.f0 = r.f0;
                 p.pattern_idx = static_cast<int>((r.item / NCAND) % depth);
-                p.num_avg = 0;
-                {
-                    static const int navg[8] = {1, 2, 3, 4, 5, 6, 2, 3};
-                    p.num_avg = navg[p.pattern_idx];
-                }
+                static const int navg[8] = {1, 2, 3, 4, 5, 6, 2, 3};
+                p.num_avg = navg[p.pattern_idx];
                 p.nbadsync = r.nbadsync;
                 std::memset(p.message, 0, sizeof(p.message));
                 for (int b = 0; b < 77; b++) p.message[b] = (r.bits[b >> 5] >> (b & 31)) & 1u;
@@ -444,7 +459,26 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
                 }
             }
         }
+        raw.clear();
+        powers.clear();
+    };
+    // two-slot software pipeline: the kernels of group g+1 are enqueued before the host fetches group g
+    int64_t prev_g0 = -1;
+    int prev_nb = 0, cur = 0;
+    for (int64_t g0 = 0; g0 < total; g0 += group) {
+        const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
+        if (int rc = launch_group(slot[cur], d_in, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
+        if (prev_g0 >= 0) {
+            if (int rc = fetch_group(slot[cur ^ 1], prev_nb, &raw, prev_g0, &powers)) return rc;
+            process(prev_g0, prev_nb);
+        }
+        prev_g0 = g0, prev_nb = nb, cur ^= 1;
     }
+    if (int rc = fetch_group(slot[cur ^ 1], prev_nb, &raw, prev_g0, &powers)) return rc;
+    process(prev_g0, prev_nb);
+    CK(cudaStreamSynchronize(st));
+    collect_times();
+    times.kernel_launches = launches;
     return 0;
 }
 
@@ -529,8 +563,12 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
         CKD(cudaStreamSynchronize(d->stream));
         d->launches += 1;
     }
-    CKD(cudaMalloc(&d->d_counters, 4 * sizeof(int)));
-    CKD(cudaMallocHost(&d->h_counters, 4 * sizeof(int)));
+    CKD(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+    for (auto& sl : d->slot) {
+        CKD(cudaMalloc(&sl.d_counters, 4 * sizeof(int)));
+        CKD(cudaMallocHost(&sl.h_counters, 4 * sizeof(int)));
+        CKD(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
     if (cfg->read_mode == 1 && cfg->analytic_method == 1) {
         // analytic_fft.cu:32-58: raised-cosine band-pass, 1500 +- 1000 Hz, beta 0.1; DC halved, upper half zero
         std::vector<float2> tw(NFFT / 2);
@@ -643,7 +681,8 @@ int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, in
     if (int rc = dec->ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
     for (int64_t g0 = 0; g0 < total; g0 += group) {
         const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
-        if (int rc = dec->launch_group(d_samples, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
+        // alternate the two buffer slots like the decode path (same stream: groups still run in order)
+        if (int rc = dec->launch_group(dec->slot[(g0 / group) & 1], d_samples, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
     }
     return MSK144_OK;
 }
@@ -715,8 +754,8 @@ int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsampl
             fp.block0 = g0;
             fp.twiddle = dec->d_twiddle;
             fp.hfilt = dec->d_hfilt;
-            fp.out = dec->d_blocks;
-            fp.powers = dec->d_powers;
+            fp.out = dec->slot[0].d_blocks;
+            fp.powers = dec->slot[0].d_powers;
             fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, dec->stream>>>(fp);
         } else {
             FrontParams fp;
@@ -725,17 +764,17 @@ int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsampl
             fp.bpc = static_cast<int>(total);
             fp.read_mode = dec->cfg.read_mode;
             fp.block0 = g0;
-            fp.out = dec->d_blocks;
-            fp.powers = dec->d_powers;
+            fp.out = dec->slot[0].d_blocks;
+            fp.powers = dec->slot[0].d_powers;
             frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, dec->stream>>>(fp);
         }
         CK(cudaGetLastError());
         dec->launches += 1;
         if (blocks_re_im)
-            CK(cudaMemcpyAsync(blocks_re_im + static_cast<size_t>(g0) * N * 2, dec->d_blocks,
+            CK(cudaMemcpyAsync(blocks_re_im + static_cast<size_t>(g0) * N * 2, dec->slot[0].d_blocks,
                                static_cast<size_t>(nb) * N * sizeof(float2), cudaMemcpyDeviceToHost, dec->stream));
         if (powers8)
-            CK(cudaMemcpyAsync(powers8 + static_cast<size_t>(g0) * 8, dec->d_powers, static_cast<size_t>(nb) * 8 * sizeof(float),
+            CK(cudaMemcpyAsync(powers8 + static_cast<size_t>(g0) * 8, dec->slot[0].d_powers, static_cast<size_t>(nb) * 8 * sizeof(float),
                                cudaMemcpyDeviceToHost, dec->stream));
         CK(cudaStreamSynchronize(dec->stream));
     }
@@ -753,37 +792,37 @@ int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nbl
     std::vector<QueueRec> hq;
     for (int64_t g0 = 0; g0 < nblocks; g0 += group) {
         const int nb = static_cast<int>(std::min<int64_t>(group, nblocks - g0));
-        CK(cudaMemcpyAsync(dec->d_blocks, blocks_re_im + static_cast<size_t>(g0) * N * 2,
+        CK(cudaMemcpyAsync(dec->slot[0].d_blocks, blocks_re_im + static_cast<size_t>(g0) * N * 2,
                            static_cast<size_t>(nb) * N * sizeof(float2), cudaMemcpyHostToDevice, dec->stream));
-        CK(cudaMemsetAsync(dec->d_counters, 0, 4 * sizeof(int), dec->stream));
+        CK(cudaMemsetAsync(dec->slot[0].d_counters, 0, 4 * sizeof(int), dec->stream));
         ScanParams sp;
-        sp.blocks = dec->d_blocks;
+        sp.blocks = dec->slot[0].d_blocks;
         sp.mix = dec->d_mix;
         sp.nf = dec->nf;
         sp.depth = dec->depth;
         sp.thr = dec->cfg.nbadsync_threshold;
-        sp.fpc = std::max(1, std::min(8, static_cast<int>((static_cast<long long>(dec->nf) * nb) / (dec->sm_count * 8))));
+        sp.fpc = dec->scan_fpc(nb);
         sp.center = dec->cfg.center_frequency_hz;
         sp.if1 = dec->if1;
         sp.step = dec->cfg.search_step_hz;
         sp.block0 = 0;
-        sp.cands = dec->d_cands;
-        sp.queue = dec->d_queue;
-        sp.queue_count = dec->d_counters;
+        sp.cands = dec->slot[0].d_cands;
+        sp.queue = dec->slot[0].d_queue;
+        sp.queue_count = dec->slot[0].d_counters;
         sp.queue_cap = static_cast<int>(static_cast<size_t>(nb) * dec->items);
         dim3 sgrid((dec->nf + sp.fpc - 1) / sp.fpc, nb);
         launch_scan(dec->depth, sgrid, dec->stream, sp);
         CK(cudaGetLastError());
         dec->launches += 1;
-        CK(cudaMemcpyAsync(dec->h_counters, dec->d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, dec->stream));
+        CK(cudaMemcpyAsync(dec->slot[0].h_counters, dec->slot[0].d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, dec->stream));
         if (cands)
-            CK(cudaMemcpyAsync(cands + static_cast<size_t>(g0) * dec->items, dec->d_cands,
+            CK(cudaMemcpyAsync(cands + static_cast<size_t>(g0) * dec->items, dec->slot[0].d_cands,
                                static_cast<size_t>(nb) * dec->items * sizeof(CandRec), cudaMemcpyDeviceToHost, dec->stream));
         CK(cudaStreamSynchronize(dec->stream));
-        const int qn = dec->h_counters[0];
+        const int qn = dec->slot[0].h_counters[0];
         if (llr || llr_item) {
             hq.resize(qn);
-            CK(cudaMemcpy(hq.data(), dec->d_queue, static_cast<size_t>(qn) * sizeof(QueueRec), cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(hq.data(), dec->slot[0].d_queue, static_cast<size_t>(qn) * sizeof(QueueRec), cudaMemcpyDeviceToHost));
             for (int i = 0; i < qn; i++) {
                 const size_t row = total_llr + i;
                 if (row >= llr_cap) {
@@ -820,7 +859,7 @@ int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t nc
     lp.flat_out = reinterpret_cast<uint4*>(d_out);
     dec->fill_ldpc_tables(&lp);
     const size_t npairs = (ncw + 1) / 2;
-    const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * 2, (npairs + LDPC_WARPS - 1) / LDPC_WARPS));
+    const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * LDPC_CTAS_PER_SM, (npairs + LDPC_WARPS - 1) / LDPC_WARPS));
     if (grid > 0) {
         ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
         CK(cudaGetLastError());
