@@ -184,6 +184,7 @@ struct msk144_decoder {
         for (int k = 0; k < 4; k++) {
             volatile float r = 1.0f / dv[k];  // IEEE single division, as the exhaustive division proof assumes
             lp->pc[k] = c[k], lp->pd[k] = dv[k], lp->pr[k] = r;
+            lp->pnd[k] = -0.5f * dv[k], lp->pr2[k] = 2.0f * r;
         }
     }
     int decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
