@@ -938,7 +938,7 @@ int msk144_selftest_ldpc_math(msk144_decoder* dec, uint64_t* tanh_mismatches, ui
 #ifdef MSK_SCAN_PROF
 // debug build only: reads and clears the per-phase cycle counters of scan_kernel
 int msk144_debug_scan_prof(unsigned long long* out8) {
-    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    unsigned long long z[16] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
     cudaDeviceSynchronize();
     cudaMemcpyFromSymbol(out8, g_scan_prof, sizeof(z));
     cudaMemcpyToSymbol(g_scan_prof, z, sizeof(z));

@@ -16,12 +16,13 @@ xd = torch.from_numpy(x).to("cuda:0")
 dec = m.Decoder(max_batch_blocks=128, center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
 s = torch.cuda.Stream()
 L = m.lib()
-out = (C.c_ulonglong * 8)()
+out = (C.c_ulonglong * 16)()
 dec.run_device(xd.data_ptr(), len(x), 1, s.cuda_stream)
 L.msk144_debug_scan_prof(out)
 nb = dec.run_device(xd.data_ptr(), len(x), 1, s.cuda_stream)
 L.msk144_debug_scan_prof(out)
-names = ["prologue S1+S2a", "S2b", "S3", "S4 || S1next", "S2a next (thread 0)", "S5 (warp 0)", "barrier wait after S5", "-"]
+names = ["prologue S1+S2a", "S2b", "S3", "S4 phase: barrier wait", "S2a next (thread 0)", "S5 (warp 0)", "barrier wait after S5",
+         "S4: slice maxima", "S4: hypot", "S4: top-8 replay", "S4: shuffles, atan2, sincos", "S4: soft bit 0", "-", "-", "-", "-"]
 tot = sum(out)
 items = nb * 501
 for n, v in zip(names, out):
