@@ -267,8 +267,17 @@ def main():
                      "ldpc_kernel": ldpc_flops_max}
         ach_gbs = bytes_alg[dom] / dur[dom] / 1e9
         ach_tf = flops_alg[dom] / dur[dom] / 1e12
+        # dram__bytes_read + dram__bytes_write of the dominant kernel from the committed `ncu --set full` capture
+        # (one 128-block launch group of this workload), scaled to this run's average launch
+        traffic = None
+        try:
+            tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+            traffic = tj["dram_bytes_per_launch"][dom] * (nblocks / max(1, groups // args.steps)) / tj["blocks_per_launch"]
+        except Exception:  # noqa: BLE001
+            pass
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ach_gbs / hbm_peak, "traffic": None, "peak_source": peak_src,
+                    "frac": ach_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes_per_launch": bytes_alg[dom] / max(1, groups // args.steps),
+                    "traffic_source": "profiles/ncu_traffic.json", "peak_source": peak_src,
                     "launches_per_step": groups // args.steps, "avg_launch_ms": per[dom] / groups,
                     "binding": "fp32 issue (not HBM: algorithmic HBM traffic is ~0.5 KB per codeword / 41 KB per block)",
                     "fp32": {"achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach_tf / fp32_peak,

@@ -946,6 +946,16 @@ int msk144_debug_scan_prof(unsigned long long* out8) {
 }
 #endif
 
+#ifdef MSK_LDPC_PROF
+int msk144_debug_ldpc_prof(unsigned long long* out8) {
+    unsigned long long z[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    cudaDeviceSynchronize();
+    cudaMemcpyFromSymbol(out8, g_ldpc_prof, sizeof(z));
+    cudaMemcpyToSymbol(g_ldpc_prof, z, sizeof(z));
+    return 0;
+}
+#endif
+
 int msk144_decode_message(const uint8_t* msg77, char* text) {
     std::string s;
     const bool ok = mskhost::decode_message(msg77, &s);

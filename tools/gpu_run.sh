@@ -23,7 +23,7 @@ for step in "$@"; do
     ncu_full)
       CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
       $CMD > gpurun_out/ncu_plain2.log 2>&1 &&
-      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 3 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
+      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 0 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
       echo "ncu_full rc=$?"; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/*.ncu-rep ;;
     *) echo "unknown step $step" ;;
   esac
