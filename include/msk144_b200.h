@@ -36,7 +36,8 @@ enum {
     MSK144_ECUDA = -2,   /* CUDA runtime error (the reference throws std::runtime_error) */
     MSK144_ENODEV = -3,  /* no usable GPU */
     MSK144_ENOMEM = -4,
-    MSK144_EOVERFLOW = -5 /* an output array was too small; counts are still returned */
+    MSK144_EOVERFLOW = -5, /* an output array was too small; counts are still returned */
+    MSK144_EAGAIN = -6     /* more input bytes are needed to decide (msk144_wav_data_offset) */
 };
 
 /* flags */
@@ -44,7 +45,11 @@ enum {
     /* Reproduce the reference's decode_cache comparator quirk (main.cu:430-447): within one block every
      * candidate after the first decoded one is reported with the FIRST candidate's text.  The CLI sets
      * it (output identical to the reference); clear it for per-payload text. */
-    MSK144_FLAG_COMPAT_DECODE_CACHE = 1
+    MSK144_FLAG_COMPAT_DECODE_CACHE = 1,
+    /* Streaming surface only: if the pushed stream starts with a RIFF/WAVE header, skip to the first byte of
+     * its "data" chunk instead of decoding the header as samples (the reference does the latter: README.md:62
+     * pipes demo/0001.wav straight in).  Off by default for compatibility; the CLI sets it for --wav. */
+    MSK144_FLAG_SKIP_WAV_HEADER = 2
 };
 
 /* The seven CLI values of main.cu:124-133 + placement.  Zero-initialise, then msk144_config_defaults(). */
@@ -191,6 +196,43 @@ int msk144_selftest_ldpc_math(msk144_decoder* dec, uint64_t* tanh_mismatches, ui
 int msk144_decode_message(const uint8_t* msg77, char* text);
 /* main.cu:406-419 line format; date14 = "%Y%m%d%H%M%S" local time, NULL = now. Returns length. */
 int msk144_format_line(const msk144_line* line, const char* date14, char* out, size_t cap);
+
+
+/* ---- adapters either side of the path (no counterpart in the reference) -------- */
+/* Pluggable text seam == f_interop.cpp:61-71: the reference resolves `__packjt77_MOD_unpack77` of a gfortran-built
+ * WSJT-X at link time (bpdecode.dll via LoadLibrary on Win32, f_interop.cpp:40-53).  Here the built-in C++ unpack77 is
+ * the default; this call (or the environment variable MSK144_UNPACK77_LIB, read at the first text decode) dlopen()s a
+ * user-supplied shared library exporting that symbol and routes every text decode through it.  NULL = built-in. */
+int msk144_set_unpack77_library(const char* path);
+/* 1 if an external unpack77 is active. */
+int msk144_unpack77_is_external(void);
+
+/* RIFF/WAVE header recognition on the first bytes of a stream.  Returns the byte offset of the first sample of the
+ * "data" chunk (> 0), 0 if the bytes are not a RIFF file (raw samples), MSK144_EAGAIN if the header is not complete
+ * within `n` bytes, MSK144_EINVAL for a RIFF file that is not PCM.  channels / sample_rate / bits may be NULL. */
+int64_t msk144_wav_data_offset(const void* bytes, size_t n, int32_t* channels, int32_t* sample_rate, int32_t* bits);
+
+/* One decode line as a JSON object on one line (machine-readable twin of msk144_format_line). Returns length. */
+int msk144_format_line_json(const msk144_line* line, const char* date14, char* out, size_t cap);
+
+/* Cross-block aggregation: the reference prints a message once per 216 ms block it decodes in (blocks overlap by
+ * half, main.cu:284-288), so one ping yields several lines.  An event merges the lines of one (channel, text) whose
+ * blocks are at most max_gap_blocks apart and carries the best line (lowest num_avg, then nbadsync, then highest snr). */
+typedef struct msk144_event {
+    int64_t first_block, last_block;
+    int32_t nlines;
+    int32_t reserved;
+    msk144_line best;
+} msk144_event;
+typedef struct msk144_aggregator msk144_aggregator;
+int msk144_aggregator_create(int32_t max_gap_blocks, msk144_aggregator** out);
+void msk144_aggregator_destroy(msk144_aggregator* agg);
+/* lines of each channel in block order (as msk144_poll / msk144_decode_* deliver them) */
+int msk144_aggregator_add(msk144_aggregator* agg, const msk144_line* lines, size_t n);
+/* events that can no longer grow: last_block + max_gap_blocks < next_block (the index of the next block the
+ * stream will produce), or all of them if flush != 0 */
+int msk144_aggregator_poll(msk144_aggregator* agg, int64_t next_block, int flush, msk144_event* out, size_t cap,
+                           size_t* nout);
 
 #ifdef __cplusplus
 }

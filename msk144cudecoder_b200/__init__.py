@@ -23,12 +23,15 @@ CLI_PATH = os.path.join(_HERE, "bin", "msk144cudecoder")
 
 BLOCK_SAMPLES, HOP_SAMPLES = 5184, 2592
 FLAG_COMPAT_DECODE_CACHE = 1
+FLAG_SKIP_WAV_HEADER = 2
 
 EXPORTED_SYMBOLS = [
     "msk144_last_error", "msk144_config_defaults", "msk144_create", "msk144_destroy", "msk144_get_info",
     "msk144_get_stage_times", "msk144_push", "msk144_poll", "msk144_reset_stream", "msk144_decode_host",
     "msk144_decode_device", "msk144_run_device", "msk144_frontend_host", "msk144_scan_host",
     "msk144_ldpc_decode_host", "msk144_ldpc_decode_device", "msk144_decode_message", "msk144_format_line",
+    "msk144_set_unpack77_library", "msk144_unpack77_is_external", "msk144_wav_data_offset", "msk144_format_line_json",
+    "msk144_aggregator_create", "msk144_aggregator_destroy", "msk144_aggregator_add", "msk144_aggregator_poll",
 ]
 
 
@@ -47,6 +50,11 @@ class Line(C.Structure):
     _fields_ = [("block_index", C.c_int64), ("channel", C.c_int32), ("snr", C.c_int32), ("f0", C.c_float),
                 ("num_avg", C.c_int32), ("nbadsync", C.c_int32), ("pattern_idx", C.c_int32),
                 ("payload", C.c_uint8 * 80), ("text", C.c_char * 40)]
+
+
+class Event(C.Structure):
+    _fields_ = [("first_block", C.c_int64), ("last_block", C.c_int64), ("nlines", C.c_int32), ("reserved", C.c_int32),
+                ("best", Line)]
 
 
 class Info(C.Structure):
@@ -111,6 +119,15 @@ def lib():
         L.msk144_decode_message.argtypes = [vp, C.c_char_p]
         L.msk144_format_line.argtypes = [C.POINTER(Line), C.c_char_p, C.c_char_p, sz]
         L.msk144_unpack77_reset.argtypes = []
+        L.msk144_set_unpack77_library.argtypes = [C.c_char_p]
+        L.msk144_wav_data_offset.argtypes = [vp, sz, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+        L.msk144_wav_data_offset.restype = C.c_int64
+        L.msk144_format_line_json.argtypes = [C.POINTER(Line), C.c_char_p, C.c_char_p, sz]
+        L.msk144_aggregator_create.argtypes = [C.c_int32, C.POINTER(vp)]
+        L.msk144_aggregator_destroy.argtypes = [vp]
+        L.msk144_aggregator_destroy.restype = None
+        L.msk144_aggregator_add.argtypes = [vp, C.POINTER(Line), sz]
+        L.msk144_aggregator_poll.argtypes = [vp, C.c_int64, C.c_int, C.POINTER(Event), sz, C.POINTER(sz)]
         _lib = L
     return _lib
 
@@ -131,7 +148,7 @@ class Decoder:
 
     def __init__(self, center: Optional[float] = None, width: float = 200.0, step: float = 2.0, depth: int = 4,
                  thr: int = 1, read_mode: int = 1, method: int = 2, device: int = 0, max_batch_blocks: int = 128,
-                 compat_cache: bool = True):
+                 compat_cache: bool = True, flags: int = 0):
         L = lib()
         cfg = Config()
         L.msk144_config_defaults(C.byref(cfg))
@@ -139,7 +156,7 @@ class Decoder:
         cfg.search_width_hz, cfg.search_step_hz, cfg.scan_depth = width, step, depth
         cfg.nbadsync_threshold, cfg.read_mode, cfg.analytic_method = thr, read_mode, method
         cfg.device, cfg.max_batch_blocks = device, max_batch_blocks
-        cfg.flags = FLAG_COMPAT_DECODE_CACHE if compat_cache else 0
+        cfg.flags = (FLAG_COMPAT_DECODE_CACHE if compat_cache else 0) | flags
         self.cfg = cfg
         self._h = C.c_void_p()
         _check(L.msk144_create(C.byref(cfg), C.byref(self._h)))
@@ -306,6 +323,69 @@ def format_line(d: dict, date: Optional[str] = None) -> str:
     buf = C.create_string_buffer(256)
     lib().msk144_format_line(C.byref(l), date.encode() if date else None, buf, 256)
     return buf.value.decode("ascii")
+
+
+def _line_struct(d: dict) -> Line:
+    l = Line()
+    l.block_index, l.channel = d.get("block", 0), d.get("channel", 0)
+    l.snr, l.f0, l.num_avg, l.nbadsync, l.pattern_idx = d["snr"], d["f0"], d["num_avg"], d["nbadsync"], d["pattern_idx"]
+    l.text = d["text"].encode("ascii")
+    pl = d.get("payload")
+    if pl is not None:
+        C.memmove(l.payload, bytes(pl), min(80, len(pl)))
+    return l
+
+
+def format_line_json(d: dict, date: Optional[str] = None) -> str:
+    """Machine-readable twin of format_line (one JSON object per line)."""
+    buf = C.create_string_buffer(512)
+    lib().msk144_format_line_json(C.byref(_line_struct(d)), date.encode() if date else None, buf, 512)
+    return buf.value.decode("ascii")
+
+
+def wav_data_offset(head: bytes):
+    """(offset, channels, sample_rate, bits): offset > 0 = first sample byte of a RIFF/WAVE file, 0 = raw samples,
+    -6 = need more bytes, -1 = RIFF but not PCM."""
+    ch, sr, bits = C.c_int32(0), C.c_int32(0), C.c_int32(0)
+    off = lib().msk144_wav_data_offset(head, len(head), C.byref(ch), C.byref(sr), C.byref(bits))
+    return int(off), ch.value, sr.value, bits.value
+
+
+def set_unpack77_library(path: Optional[str]) -> bool:
+    """Route text decoding through a library exporting __packjt77_MOD_unpack77 (None = built-in)."""
+    return lib().msk144_set_unpack77_library(path.encode() if path else None) == 0
+
+
+class Aggregator:
+    """One event per ping: merges the per-block repeats of a (channel, text) at most `max_gap` blocks apart."""
+
+    def __init__(self, max_gap: int = 2):
+        self._h = C.c_void_p()
+        _check(lib().msk144_aggregator_create(max_gap, C.byref(self._h)))
+
+    def add(self, lines: List[dict]):
+        arr = (Line * max(1, len(lines)))(*[_line_struct(l) for l in lines])
+        _check(lib().msk144_aggregator_add(self._h, arr, len(lines)))
+
+    def poll(self, next_block: int = 0, flush: bool = False) -> List[dict]:
+        out, n, ev = [], C.c_size_t(0), (Event * 256)()
+        while True:
+            _check(lib().msk144_aggregator_poll(self._h, next_block, 1 if flush else 0, ev, 256, C.byref(n)))
+            out += [dict(_line_dict(ev[i].best), first_block=int(ev[i].first_block), last_block=int(ev[i].last_block),
+                         nlines=int(ev[i].nlines)) for i in range(n.value)]
+            if n.value < 256:
+                return out
+
+    def close(self):
+        if self._h:
+            lib().msk144_aggregator_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
 
 
 def reset_hash_tables():

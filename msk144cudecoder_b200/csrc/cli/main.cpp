@@ -34,6 +34,10 @@ static void show_help(const char* prog) {
     std::cout << "                   --device=0                  CUDA device ordinal." << std::endl;
     std::cout << "                   --batch-blocks=128          Blocks per GPU launch group when input arrives faster than real time." << std::endl;
     std::cout << "                   --per-payload-text          Decode every payload's own text (the reference reuses the first decode of a block)." << std::endl;
+    std::cout << "                   --wav                       Skip a RIFF/WAVE header at the start of stdin (the reference decodes it as samples)." << std::endl;
+    std::cout << "                   --json                      One JSON object per line instead of the '***' line format." << std::endl;
+    std::cout << "                   --dedupe[=2]                One line per ping: merge the per-block repeats of a message at most N blocks apart." << std::endl;
+    std::cout << "                   --unpack77-lib=PATH         Text decoding through a library exporting __packjt77_MOD_unpack77 (gfortran-built WSJT-X)." << std::endl;
     // clang-format on
 }
 
@@ -47,7 +51,8 @@ int main(int argc, char* const argv[]) {
     msk144_config cfg;
     msk144_config_defaults(&cfg);
     cfg.flags = MSK144_FLAG_COMPAT_DECODE_CACHE;
-    bool center_set = false;
+    bool center_set = false, json = false;
+    int dedupe_gap = -1;  // < 0: print every per-block line, as the reference does
     static struct option long_options[] = {{"help", no_argument, 0, 0},                     // 0
                                            {"center-frequency", required_argument, 0, 0},   // 1
                                            {"search-step", required_argument, 0, 0},        // 2
@@ -59,6 +64,10 @@ int main(int argc, char* const argv[]) {
                                            {"device", required_argument, 0, 0},             // 8
                                            {"batch-blocks", required_argument, 0, 0},       // 9
                                            {"per-payload-text", no_argument, 0, 0},         // 10
+                                           {"wav", no_argument, 0, 0},                      // 11
+                                           {"json", no_argument, 0, 0},                     // 12
+                                           {"dedupe", optional_argument, 0, 0},             // 13
+                                           {"unpack77-lib", required_argument, 0, 0},       // 14
                                            {0, 0, 0, 0}};
     while (true) {
         int option_index = 0;
@@ -77,6 +86,15 @@ int main(int argc, char* const argv[]) {
             case 8: cfg.device = atoi(optarg); break;
             case 9: cfg.max_batch_blocks = atoi(optarg); break;
             case 10: cfg.flags &= ~MSK144_FLAG_COMPAT_DECODE_CACHE; break;
+            case 11: cfg.flags |= MSK144_FLAG_SKIP_WAV_HEADER; break;
+            case 12: json = true; break;
+            case 13: dedupe_gap = optarg ? atoi(optarg) : 2; break;
+            case 14:
+                if (msk144_set_unpack77_library(optarg) != 0) {
+                    std::cerr << "Cannot load __packjt77_MOD_unpack77 from " << optarg << std::endl;
+                    return 2;
+                }
+                break;
             default: show_help(argv[0]); return 0;
         }
     }
@@ -117,6 +135,23 @@ int main(int argc, char* const argv[]) {
     std::vector<msk144_line> lines(4096);
     size_t total_bytes = 0;
     int rc_exit = 0;
+    msk144_aggregator* agg = nullptr;
+    if (dedupe_gap >= 0) msk144_aggregator_create(dedupe_gap, &agg);
+    std::vector<msk144_event> events(1024);
+    int64_t blocks_done = 0;
+    auto print_line = [&](const msk144_line& l) {
+        char out[512];
+        if (json) msk144_format_line_json(&l, nullptr, out, sizeof(out));
+        else msk144_format_line(&l, nullptr, out, sizeof(out));
+        std::cout << out << std::endl;
+    };
+    auto drain_events = [&](int flush) {
+        size_t ne = 0;
+        do {
+            msk144_aggregator_poll(agg, blocks_done, flush, events.data(), events.size(), &ne);
+            for (size_t i = 0; i < ne; i++) print_line(events[i].best);
+        } while (ne == events.size());
+    };
     while (true) {
         // read() returns what is available: real-time input is processed block by block, a file or a
         // fast pipe is processed in large launch groups.
@@ -139,12 +174,15 @@ int main(int argc, char* const argv[]) {
         size_t got = 0;
         do {
             msk144_poll(dec, lines.data(), lines.size(), &got);
-            for (size_t i = 0; i < got; i++) {
-                char out[256];
-                msk144_format_line(&lines[i], nullptr, out, sizeof(out));
-                std::cout << out << std::endl;
-            }
+            if (agg) msk144_aggregator_add(agg, lines.data(), got);
+            else for (size_t i = 0; i < got; i++) print_line(lines[i]);
         } while (got == lines.size());
+        if (agg) {
+            // blocks completed so far (WAV header bytes, if any, make this an upper bound by < 1 block: harmless,
+            // an event is only held back a little longer)
+            blocks_done = total_bytes >= block_bytes ? static_cast<int64_t>((total_bytes - block_bytes) / hop_bytes) + 1 : 0;
+            drain_events(0);
+        }
         const double ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t0).count();
         const double blocks_in = static_cast<double>(n) / hop_bytes;
         if (blocks_in >= 1.0 && ms > 210.0 * blocks_in)  // main.cu:397-403, scaled to the group size
@@ -156,6 +194,10 @@ int main(int argc, char* const argv[]) {
     if (total_bytes < block_bytes) leftover = total_bytes;
     else leftover = (total_bytes - block_bytes) % hop_bytes;
     const size_t rc_items = (cfg.read_mode == 1) ? leftover / 2 : leftover;
+    if (agg) {
+        drain_events(1);
+        msk144_aggregator_destroy(agg);
+    }
     std::cerr << "Incomplete read error. rc=" << rc_items << std::endl;
     std::cout << "Done" << std::endl;
     msk144_destroy(dec);

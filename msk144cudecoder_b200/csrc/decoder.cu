@@ -157,6 +157,7 @@ struct msk144_decoder {
 
     // streaming state (msk144_push / msk144_poll)
     std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
+    bool wav_checked = false;      // MSK144_FLAG_SKIP_WAV_HEADER: the start of the stream has been examined
     int64_t next_block = 0;
     mskhost::SnrTracker stream_snr;
     std::deque<msk144_line> out_lines;
@@ -692,6 +693,7 @@ int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, in
 int msk144_reset_stream(msk144_decoder* dec) {
     if (!dec) return fail(MSK144_EINVAL, "null argument");
     dec->pending.clear();
+    dec->wav_checked = false;
     dec->next_block = 0;
     dec->stream_snr.reset();
     dec->out_lines.clear();
@@ -703,6 +705,14 @@ int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
     CK(cudaSetDevice(dec->cfg.device));
     const uint8_t* b = static_cast<const uint8_t*>(bytes);
     dec->pending.insert(dec->pending.end(), b, b + nbytes);
+    if ((dec->cfg.flags & MSK144_FLAG_SKIP_WAV_HEADER) && !dec->wav_checked) {
+        // start of the stream: recognise a RIFF/WAVE header and drop it (adapters.cpp)
+        const int64_t off = msk144_wav_data_offset(dec->pending.data(), dec->pending.size(), nullptr, nullptr, nullptr);
+        if (off == MSK144_EAGAIN) return MSK144_OK;  // header not complete yet
+        if (off == MSK144_EINVAL) return fail(MSK144_EINVAL, "RIFF input is not PCM");
+        dec->wav_checked = true;
+        if (off > 0) dec->pending.erase(dec->pending.begin(), dec->pending.begin() + off);
+    }
     const size_t nsamp = dec->pending.size() / 2;
     if (nsamp < static_cast<size_t>(N)) return MSK144_OK;
     const size_t nblocks = (nsamp - N) / (N / 2) + 1;

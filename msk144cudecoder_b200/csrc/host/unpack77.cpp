@@ -12,8 +12,11 @@
 // as in WSJT-X (nrx=1 receive semantics; no "my call"/"dx call" is ever set by the reference).
 #include "unpack77.h"
 
+#include <dlfcn.h>
+
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -362,12 +365,65 @@ bool unpack77_impl(const char* c77, int /*nrx*/, std::string* msg) {
     return ok;
 }
 
+
+
+// ---- pluggable seam (f_interop.cpp:10-29,61-71): a gfortran-built WSJT-X library exporting the module procedure
+typedef void (*unpack77_fn)(char*, const int*, char*, int*, size_t, size_t);
+unpack77_fn g_ext = nullptr;
+void* g_ext_handle = nullptr;
+bool g_env_checked = false;
+
+int load_external(const char* path) {  // g_mu held
+    if (g_ext_handle) dlclose(g_ext_handle);
+    g_ext_handle = nullptr, g_ext = nullptr;
+    if (!path || !*path) return 0;
+    void* h = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+    if (!h) return -1;
+    // dlsym on the handle searches that library (and its dependencies), not this one, so the user's symbol wins
+    // over the alias exported below
+    void* f = dlsym(h, "__packjt77_MOD_unpack77");
+    if (!f) {
+        dlclose(h);
+        return -1;
+    }
+    g_ext_handle = h;
+    g_ext = reinterpret_cast<unpack77_fn>(f);
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
 
+int msk144_set_unpack77_library(const char* path) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    g_env_checked = true;  // an explicit choice overrides the environment
+    return load_external(path) == 0 ? 0 : -1;
+}
+
+int msk144_unpack77_is_external(void) {
+    std::lock_guard<std::mutex> lk(g_mu);
+    return g_ext ? 1 : 0;
+}
+
 void msk144_unpack77(const char c77[77], const int* nrx, char msg[37], int* ok) {
     std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_env_checked) {
+        g_env_checked = true;
+        if (const char* e = std::getenv("MSK144_UNPACK77_LIB")) {
+            if (load_external(e) != 0) std::fprintf(stderr, "msk144: cannot use MSK144_UNPACK77_LIB=%s, built-in unpack77 stays\n", e);
+        }
+    }
+    if (g_ext) {
+        char in[77];
+        std::memcpy(in, c77, 77);
+        const int one = 1;
+        int okv = 0;  // Fortran LOGICAL, 4 bytes
+        std::memset(msg, ' ', 37);
+        g_ext(in, nrx ? nrx : &one, msg, &okv, 77, 37);
+        *ok = okv ? 1 : 0;
+        return;
+    }
     std::string s;
     const bool r = unpack77_impl(c77, nrx ? *nrx : 1, &s);
     std::memset(msg, ' ', 37);

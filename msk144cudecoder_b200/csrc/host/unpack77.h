@@ -9,6 +9,10 @@ extern "C" {
 void msk144_unpack77(const char c77[77], const int* nrx, char msg[37], int* ok);
 // Forget all hashed call signs (the tables otherwise persist for the life of the process).
 void msk144_unpack77_reset(void);
+// Route text decoding through a user-supplied library exporting __packjt77_MOD_unpack77 (NULL / "" = built-in).
+// Returns 0, or -1 if the library or the symbol cannot be loaded (the built-in stays active).
+int msk144_set_unpack77_library(const char* path);
+int msk144_unpack77_is_external(void);
 // gfortran-ABI alias so that code written against WSJT-X links unchanged.
 void __packjt77_MOD_unpack77(char c77[], const int* nrx, char msg[], int* ok, size_t len77, size_t len37);
 #ifdef __cplusplus

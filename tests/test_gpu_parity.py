@@ -198,3 +198,57 @@ def test_empty_and_short_inputs(gpu):
         assert d.decode_host(np.zeros(5183, np.int16))[0] == []
         lines, res = d.decode_host(np.zeros(5184, np.int16))     # all-zero block: rms 0 -> NaNs, no decode, no crash
         assert lines == [] and len(res) == 0
+
+
+def test_cli_wav_json_dedupe(gpu, synth):
+    """Extensions either side of the path: a RIFF header is skipped with --wav (and decoded as 22 samples
+    without it, as the reference does); --json carries the same fields; --dedupe prints one line per ping."""
+    import json
+    import re
+    import struct
+    x, pings = synth.cfg1_demo(seconds=12.0, seed=1)
+    raw = x.tobytes()
+    fmt = struct.pack("<HHIIHH", 1, 1, 12000, 24000, 2, 16)
+    wav = b"RIFF" + struct.pack("<I", 36 + len(raw)) + b"WAVE" + b"fmt " + struct.pack("<I", 16) + fmt + b"data" + \
+        struct.pack("<I", len(raw)) + raw
+    base = [gpu.CLI_PATH, "--search-width=100", "--scan-depth=3"]
+    run = lambda extra, data: subprocess.run(base + extra, input=data, capture_output=True).stdout.decode().splitlines()
+    mask = lambda ls: [re.sub(r"date=\d{14}", "date=x", l) for l in ls]
+    plain = run([], raw)
+    assert plain[-1] == "Done" and len(plain) > 3
+    assert mask(run(["--wav"], wav)) == mask(plain)          # header skipped: identical to the raw stream
+    assert mask(run(["--wav"], raw)) == mask(plain)          # --wav on headerless input changes nothing
+    js = [json.loads(l) for l in run(["--json"], raw)[:-1]]
+    assert len(js) == len(plain) - 1
+    for j, l in zip(js, plain):
+        m = re.search(r"snr=\s*(-?\d+); f0=\s*([-\d.e+]+); num_avg=(\d+); nbadsync=(\d+); pattern_idx=(\d+);.*msg='(.*)';", l)
+        assert (j["snr"], j["num_avg"], j["nbadsync"], j["pattern_idx"], j["msg"]) == \
+            (int(m.group(1)), int(m.group(2 + 1)), int(m.group(4)), int(m.group(5)), m.group(6))
+        assert abs(j["f0"] - float(m.group(2))) < 1e-3 and len(j["payload"]) == 77
+    dd = run(["--dedupe", "--json"], raw)
+    assert dd[-1] == "Done"
+    ev = [json.loads(l) for l in dd[:-1]]
+    # one event per ping (cfg1_demo: 8 pings of distinct start times; a text may be sent by more than one ping)
+    assert len(ev) < len(js) and {e["msg"] for e in ev} == {j["msg"] for j in js}
+    for e in ev:
+        assert any(all(j[k] == e[k] for k in ("block", "msg", "num_avg", "nbadsync", "snr")) for j in js)
+        near = [j for j in js if j["msg"] == e["msg"] and abs(j["block"] - e["block"]) <= 2]   # same event for sure
+        assert (e["num_avg"], e["nbadsync"]) == min((j["num_avg"], j["nbadsync"]) for j in near)
+
+
+def test_push_skips_wav_header_when_asked(gpu, synth):
+    import struct
+    x, _ = synth.cfg1_demo(seconds=6.0, seed=1)
+    raw = x.tobytes()
+    hdr = b"RIFF" + struct.pack("<I", 36 + len(raw)) + b"WAVE" + b"fmt " + struct.pack("<I", 16) + \
+        struct.pack("<HHIIHH", 1, 1, 12000, 24000, 2, 16) + b"data" + struct.pack("<I", len(raw))
+    with gpu.Decoder(width=100, step=2, depth=3, thr=1) as d:
+        want, _ = d.decode_host(x)
+    with gpu.Decoder(width=100, step=2, depth=3, thr=1, flags=gpu.FLAG_SKIP_WAV_HEADER) as d:
+        got = []
+        data = hdr + raw
+        for i in range(0, 70, 7):               # the header arrives in fragments
+            d.push(data[i:i + 7])
+        d.push(data[70:])
+        got += d.poll(4096)
+    assert lines_key(got) == lines_key(want)

@@ -13,6 +13,8 @@ for step in "$@"; do
     golden) timeout 900 python tools/make_golden.py gpurun_out/golden > gpurun_out/golden.log 2>&1; echo "golden rc=$?"; tail -12 gpurun_out/golden.log ;;
     bench)  timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.log; tail -5 gpurun_out/bench.err ;;
     benchref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2> gpurun_out/bench_ref.err; echo "benchref rc=$?"; tail -3 gpurun_out/bench_ref.log; tail -5 gpurun_out/bench_ref.err ;;
+    configs) timeout 1200 python tools/bench_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"; cut -c1-600 gpurun_out/configs.jsonl; tail -5 gpurun_out/configs.err ;;
+    fullsize) timeout 1500 python -m pytest tests/test_gpu_fullsize.py -m gpu -q --timeout=900 > gpurun_out/pytest_fullsize.log 2>&1; echo "fullsize rc=$?"; tail -40 gpurun_out/pytest_fullsize.log ;;
     stages) timeout 600 python tools/bench_stages.py > gpurun_out/stages.log 2>&1; echo "stages rc=$?"; cat gpurun_out/stages.log | cut -c1-400 ;;
     quick)  timeout 900 python -m pytest tests/test_golden.py tests/test_gpu_parity.py -m gpu -q -x --timeout=600 -k "ldpc or cli or stream_lines" > gpurun_out/pytest_quick.log 2>&1; echo "quick rc=$?"; tail -5 gpurun_out/pytest_quick.log ;;
     ncu_list)
