@@ -157,6 +157,7 @@ struct msk144_decoder {
 
     // streaming state (msk144_push / msk144_poll)
     std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
+    int share_twins = std::getenv("MSK144_NO_TWINS") ? 0 : 1;  // A/B knob; results are identical either way
     bool wav_checked = false;      // MSK144_FLAG_SKIP_WAV_HEADER: the start of the stream has been examined
     int64_t next_block = 0;
     mskhost::SnrTracker stream_snr;
@@ -331,6 +332,7 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
     sp.queue = sl.d_queue;
     sp.queue_count = sl.d_counters;
     sp.queue_cap = static_cast<int>(std::min<size_t>(queue_cap, static_cast<size_t>(nb) * items));
+    sp.share_twins = share_twins;
     dim3 sgrid((nf + sp.fpc - 1) / sp.fpc, nb);
     launch_scan(depth, sgrid, st, sp);
     CK(cudaGetLastError());
@@ -821,6 +823,7 @@ int msk144_scan_host(msk144_decoder* dec, const float* blocks_re_im, int64_t nbl
         sp.queue = dec->slot[0].d_queue;
         sp.queue_count = dec->slot[0].d_counters;
         sp.queue_cap = static_cast<int>(static_cast<size_t>(nb) * dec->items);
+        sp.share_twins = 0;  // the stage API returns every gated candidate's own LLR row
         dim3 sgrid((dec->nf + sp.fpc - 1) / sp.fpc, nb);
         launch_scan(dec->depth, sgrid, dec->stream, sp);
         CK(cudaGetLastError());

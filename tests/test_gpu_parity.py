@@ -252,3 +252,22 @@ def test_push_skips_wav_header_when_asked(gpu, synth):
         d.push(data[70:])
         got += d.poll(4096)
     assert lines_key(got) == lines_key(want)
+
+
+def test_twin_sharing_is_invisible(gpu, synth, monkeypatch):
+    """A candidate at pos >= 5184 whose twin pos - 5184 sits in the same list has bit-identical soft bits; the pipeline
+    decodes one of the two and reports both.  Every LDPC success record must be the same with the sharing off."""
+    x, _ = synth.cfg2_deep_audio(seconds=12.0, seed=144, npings=24)
+    kw = dict(center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
+    with gpu.Decoder(**kw) as d:
+        lines, res = d.decode_host(x, result_cap=1 << 18)
+        ncw = d.stage_times()["llr_codewords"]
+    monkeypatch.setenv("MSK144_NO_TWINS", "1")
+    with gpu.Decoder(**kw) as d:
+        lines0, res0 = d.decode_host(x, result_cap=1 << 18)
+        ncw0 = d.stage_times()["llr_codewords"]
+    order = ["block_index", "item_index"]
+    assert len(res) > 0 and np.array_equal(np.sort(res, order=order), np.sort(res0, order=order))
+    assert lines_key(lines) == lines_key(lines0)
+    assert 0.9 * ncw0 < ncw < ncw0                      # a few per cent fewer codewords reach the LDPC stage
+    assert (res["pos"] >= 5184).any()                   # and twins are among the successes
