@@ -875,7 +875,13 @@ int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t nc
     const size_t npairs = (ncw + 1) / 2;
     const int grid = static_cast<int>(std::min<size_t>(static_cast<size_t>(dec->sm_count) * LDPC_CTAS_PER_SM, (npairs + LDPC_WARPS - 1) / LDPC_WARPS));
     if (grid > 0) {
-        ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
+        // caller-supplied LLRs: iteration counts differ from codeword to codeword, so the streaming form (each half
+        // of a warp refills on its own) is used; MSK144_LDPC_NO_REFILL=1 selects the pair form for A/B runs
+        static const bool no_refill = std::getenv("MSK144_LDPC_NO_REFILL") != nullptr;
+        if (no_refill)
+            ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
+        else
+            ldpc_stream_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
         CK(cudaGetLastError());
         dec->launches += 1;
     }
