@@ -269,10 +269,12 @@ def main():
         ach_tf = flops_alg[dom] / dur[dom] / 1e12
         # dram__bytes_read + dram__bytes_write of the dominant kernel from the committed `ncu --set full` capture
         # (one 128-block launch group of this workload), scaled to this run's average launch
-        traffic = None
+        traffic, ncu_pipes = None, None
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
             traffic = tj["dram_bytes_per_launch"][dom] * (nblocks / max(1, groups // args.steps)) / tj["blocks_per_launch"]
+            ncu_pipes = {"issue_active_pct": tj.get("issue_active_pct", {}).get(dom), **tj.get("pipe_pct", {}).get(dom, {}),
+                         "source": tj.get("source")}
         except Exception:  # noqa: BLE001
             pass
         roofline = {"bound": "hbm", "kernel": dom, "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
@@ -282,6 +284,7 @@ def main():
                     "binding": "fp32 issue (not HBM: algorithmic HBM traffic is ~0.5 KB per codeword / 41 KB per block)",
                     "fp32": {"achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach_tf / fp32_peak,
                              "peak_source": f"148 SM x 128 lanes x 2 x {sm_mhz:.0f} MHz"},
+                    "ncu_pipes_pct_of_peak": ncu_pipes,
                     "kernel_share_of_step": {k: v / max(1e-9, st["total_ms"]) for k, v in per.items()},
                     "kernel_ms_per_step": {k: v / args.steps for k, v in per.items()}}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
