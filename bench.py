@@ -281,7 +281,9 @@ def main():
                     "frac": ach_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes_per_launch": bytes_alg[dom] / max(1, groups // args.steps),
                     "traffic_source": "profiles/ncu_traffic.json", "peak_source": peak_src,
                     "launches_per_step": groups // args.steps, "avg_launch_ms": per[dom] / groups,
-                    "binding": "fp32 issue (not HBM: algorithmic HBM traffic is ~0.5 KB per codeword / 41 KB per block)",
+                    "binding": "instruction issue of a packed-FP32 / ALU / MUFU mix (not HBM: algorithmic HBM traffic is ~0.5 KB per codeword / "
+                               "41 KB per block); ldpc_kernel issues 0.625 warp instructions per cycle per scheduler against 0.73-0.78 "
+                               "measured for a dependency-free stream of the same mix (profiles/r01_v6_pipes.txt)",
                     "fp32": {"achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach_tf / fp32_peak,
                              "peak_source": f"148 SM x 128 lanes x 2 x {sm_mhz:.0f} MHz"},
                     "ncu_pipes_pct_of_peak": ncu_pipes,
