@@ -162,6 +162,16 @@ int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t samp
                          void* stream, msk144_line* lines, size_t line_cap, size_t* nlines,
                          msk144_result* results, size_t result_cap, size_t* nresults);
 
+/* Multi-channel input as a channeliser / multi-receiver front end delivers it: one sample of every channel per time
+ * step (samples[t][c], 2 bytes each).  The reference reads one channel from stdin (main.cu:261-298); this is the ingest
+ * adapter of SURVEY.md section 8f.  `_device`: transposes d_in [spc][nchan] into d_out [nchan][spc] (the layout of
+ * msk144_decode_device) on `stream`; d_in and d_out must not overlap.  `_host_interleaved`: H2D, transpose, decode. */
+int msk144_deinterleave_device(msk144_decoder* dec, const void* d_in, void* d_out, size_t samples_per_channel, int nchan,
+                               void* stream);
+int msk144_decode_host_interleaved(msk144_decoder* dec, const void* samples, size_t samples_per_channel, int nchan,
+                                   msk144_line* lines, size_t line_cap, size_t* nlines,
+                                   msk144_result* results, size_t result_cap, size_t* nresults);
+
 /* Device-only pass for measurement: runs the kernels on `stream` over resident input and leaves the
  * results on the device; no host synchronisation, no D2H.  *nblocks_out = blocks processed. */
 int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t samples_per_channel, int nchan,

@@ -31,6 +31,7 @@ EXPORTED_SYMBOLS = [
     "msk144_decode_device", "msk144_run_device", "msk144_frontend_host", "msk144_scan_host",
     "msk144_ldpc_decode_host", "msk144_ldpc_decode_device", "msk144_decode_message", "msk144_format_line",
     "msk144_set_unpack77_library", "msk144_unpack77_is_external", "msk144_wav_data_offset", "msk144_format_line_json",
+    "msk144_deinterleave_device", "msk144_decode_host_interleaved",
     "msk144_aggregator_create", "msk144_aggregator_destroy", "msk144_aggregator_add", "msk144_aggregator_poll",
 ]
 
@@ -110,6 +111,8 @@ def lib():
         L.msk144_decode_host.argtypes = [vp, vp, sz, C.c_int, C.POINTER(Line), sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
         L.msk144_decode_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(Line), sz, C.POINTER(sz), vp, sz,
                                            C.POINTER(sz)]
+        L.msk144_decode_host_interleaved.argtypes = L.msk144_decode_host.argtypes
+        L.msk144_deinterleave_device.argtypes = [vp, vp, vp, sz, C.c_int, vp]
         L.msk144_run_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(C.c_int64)]
         L.msk144_frontend_host.argtypes = [vp, vp, sz, vp, vp, C.POINTER(C.c_int64)]
         L.msk144_scan_host.argtypes = [vp, vp, C.c_int64, vp, vp, vp, sz, C.POINTER(sz)]
@@ -196,12 +199,18 @@ class Decoder:
         _check(rc)
         return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
 
-    def decode_host(self, samples: np.ndarray, nchan: int = 1, line_cap: int = 4096, result_cap: int = 1 << 16):
-        """samples: int16 (audio) or int8 I,Q pairs, `nchan` equal-length channels back to back.
+    def decode_host(self, samples: np.ndarray, nchan: int = 1, line_cap: int = 4096, result_cap: int = 1 << 16,
+                    interleaved: bool = False):
+        """samples: int16 (audio) or int8 I,Q pairs, `nchan` equal-length channels back to back, or -- with
+        interleaved=True -- one sample of every channel per time step ([t][c]).
         result_cap = 0: decode lines only (the per-candidate LDPC successes are not returned)."""
         samples = np.ascontiguousarray(samples)
         spc = samples.nbytes // 2 // nchan
-        return self._decode(lib().msk144_decode_host, samples.ctypes.data, spc, nchan, (), line_cap, result_cap)
+        fn = lib().msk144_decode_host_interleaved if interleaved else lib().msk144_decode_host
+        return self._decode(fn, samples.ctypes.data, spc, nchan, (), line_cap, result_cap)
+
+    def deinterleave_device(self, d_in: int, d_out: int, samples_per_channel: int, nchan: int, stream: int = 0):
+        _check(lib().msk144_deinterleave_device(self._h, d_in, d_out, samples_per_channel, nchan, C.c_void_p(stream)))
 
     def decode_device(self, dev_ptr: int, samples_per_channel: int, nchan: int = 1, stream: int = 0,
                       line_cap: int = 4096, result_cap: int = 1 << 16):

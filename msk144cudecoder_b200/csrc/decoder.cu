@@ -672,6 +672,42 @@ int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int
                                 nresults);
 }
 
+int msk144_deinterleave_device(msk144_decoder* dec, const void* d_in, void* d_out, size_t spc, int nchan, void* stream) {
+    if (!dec || !d_in || !d_out || nchan < 1 || d_in == d_out) return fail(MSK144_EINVAL, "bad argument");
+    if (spc == 0) return MSK144_OK;
+    CK(cudaSetDevice(dec->cfg.device));
+    cudaStream_t st = stream ? static_cast<cudaStream_t>(stream) : dec->stream;
+    const dim3 grid(static_cast<unsigned>((spc + DEINT_TILE - 1) / DEINT_TILE), static_cast<unsigned>((nchan + DEINT_TILE - 1) / DEINT_TILE));
+    if (grid.y > 65535u) return fail(MSK144_EINVAL, "too many channels");
+    const bool vec = nchan % 4 == 0 && spc % 4 == 0 && reinterpret_cast<uintptr_t>(d_in) % 8 == 0 &&
+                     reinterpret_cast<uintptr_t>(d_out) % 8 == 0;
+    const auto* in = static_cast<const unsigned short*>(d_in);
+    auto* out = static_cast<unsigned short*>(d_out);
+    if (vec)
+        deinterleave_kernel<true><<<grid, DEINT_THREADS, 0, st>>>(in, out, static_cast<long long>(spc), nchan);
+    else
+        deinterleave_kernel<false><<<grid, DEINT_THREADS, 0, st>>>(in, out, static_cast<long long>(spc), nchan);
+    CK(cudaGetLastError());
+    dec->launches += 1;
+    return MSK144_OK;
+}
+
+int msk144_decode_host_interleaved(msk144_decoder* dec, const void* samples, size_t spc, int nchan, msk144_line* lines,
+                                   size_t line_cap, size_t* nlines, msk144_result* results, size_t result_cap,
+                                   size_t* nresults) {
+    if (!dec || !samples || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    const size_t bytes = spc * static_cast<size_t>(nchan) * 2;
+    // one allocation: [channel-major copy | interleaved input]; the decode reads the first half
+    if (int rc = dec->ensure_raw(2 * bytes + 16)) return rc;
+    char* d_cm = static_cast<char*>(dec->d_raw);
+    char* d_il = d_cm + ((bytes + 15) / 16) * 16;
+    CK(cudaMemcpyAsync(d_il, samples, bytes, cudaMemcpyHostToDevice, dec->stream));
+    dec->h2d_bytes += bytes;
+    if (int rc = msk144_deinterleave_device(dec, d_il, d_cm, spc, nchan, dec->stream)) return rc;
+    return msk144_decode_device(dec, d_cm, spc, nchan, dec->stream, lines, line_cap, nlines, results, result_cap, nresults);
+}
+
 int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, int nchan, void* stream,
                       int64_t* nblocks_out) {
     if (!dec || !d_samples || nchan < 1) return fail(MSK144_EINVAL, "bad argument");

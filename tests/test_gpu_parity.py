@@ -271,3 +271,29 @@ def test_twin_sharing_is_invisible(gpu, synth, monkeypatch):
     assert lines_key(lines) == lines_key(lines0)
     assert 0.9 * ncw0 < ncw < ncw0                      # a few per cent fewer codewords reach the LDPC stage
     assert (res["pos"] >= 5184).any()                   # and twins are among the successes
+
+
+@pytest.mark.parametrize("nchan,nsamp", [(1, 5184), (3, 7777), (8, 20000), (64, 12000), (130, 6402), (1024, 5184)])
+def test_deinterleave_is_a_transpose(gpu, nchan, nsamp):
+    """[t][c] -> [c][t] for vector-friendly and ragged shapes (both code paths of deinterleave_kernel)."""
+    import torch
+    rng = np.random.default_rng(nchan * 7 + nsamp)
+    x = rng.integers(-32768, 32767, (nsamp, nchan), dtype=np.int16)
+    xin = torch.from_numpy(x).cuda()
+    out = torch.full((nchan, nsamp), 12345, dtype=torch.int16, device="cuda")
+    torch.cuda.synchronize()
+    with gpu.Decoder(width=20, depth=1) as d:
+        d.deinterleave_device(xin.data_ptr(), out.data_ptr(), nsamp, nchan)
+        torch.cuda.synchronize()
+    assert np.array_equal(out.cpu().numpy(), x.T)
+
+
+def test_interleaved_input_equals_channel_major(gpu, synth):
+    chans = [synth.cfg5_channel(c, seconds=4.0)[0] for c in range(5)]
+    cm = np.concatenate(chans)
+    il = np.stack(chans, axis=1).copy()                    # [t][c]
+    with gpu.Decoder(width=100, step=2, depth=3, thr=2) as d:
+        a, ra = d.decode_host(cm, nchan=5)
+        b, rb = d.decode_host(il, nchan=5, interleaved=True)
+    assert len(a) > 0 and a == b
+    assert np.array_equal(ra, rb)
