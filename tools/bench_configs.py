@@ -173,8 +173,30 @@ def deinterleave(nchan=1024, nsamp=720000, reps=20):
                       "hbm_peak_gbs": hbm_peak(), "hbm_frac": gbs / hbm_peak(), "correct": ok}), flush=True)
 
 
+def latency(seconds=30.0):
+    """Real-time use: one 2592-sample hop pushed at a time (what arrives every 216 ms), wall clock push -> lines polled."""
+    x, _ = synth.cfg2_deep_audio(seconds=seconds, seed=144)
+    raw = x.tobytes()
+    hop = 2592 * 2
+    for name, kw in (("deep", dict(center=1500.0, **DEEP)), ("default", dict(width=100.0, step=2.0, depth=3, thr=1))):
+        with m.Decoder(max_batch_blocks=8, **kw) as d:
+            d.push(raw[: 5184 * 2])
+            d.poll()
+            ts = []
+            for i in range(5184 * 2, len(raw) - hop + 1, hop):
+                t0 = time.perf_counter()
+                d.push(raw[i:i + hop])
+                d.poll()
+                ts.append(time.perf_counter() - t0)
+        ts = np.array(ts[3:]) * 1e3
+        print(json.dumps({"bench": "latency_per_block_" + name, "blocks": len(ts), "ms_median": float(np.median(ts)),
+                          "ms_p99": float(np.percentile(ts, 99)), "ms_max": float(ts.max()), "budget_ms": 216.0}), flush=True)
+
+
 def main():
-    which = sys.argv[1:] or ["cfg1", "cfg3", "cfg4", "cfg5", "deinterleave"]
+    which = sys.argv[1:] or ["cfg1", "cfg3", "cfg4", "cfg5", "deinterleave", "latency"]
+    if "latency" in which:
+        latency()
     if "deinterleave" in which:
         deinterleave()
     if "cfg1" in which:
