@@ -31,7 +31,7 @@ EXPORTED_SYMBOLS = [
     "msk144_decode_device", "msk144_run_device", "msk144_frontend_host", "msk144_scan_host",
     "msk144_ldpc_decode_host", "msk144_ldpc_decode_device", "msk144_decode_message", "msk144_format_line",
     "msk144_set_unpack77_library", "msk144_unpack77_is_external", "msk144_wav_data_offset", "msk144_format_line_json",
-    "msk144_deinterleave_device", "msk144_decode_host_interleaved",
+    "msk144_deinterleave_device", "msk144_decode_host_interleaved", "msk144_push_interleaved",
     "msk144_aggregator_create", "msk144_aggregator_destroy", "msk144_aggregator_add", "msk144_aggregator_poll",
 ]
 
@@ -106,6 +106,7 @@ def lib():
         L.msk144_get_info.argtypes = [vp, C.POINTER(Info)]
         L.msk144_get_stage_times.argtypes = [vp, C.POINTER(StageTimes)]
         L.msk144_push.argtypes = [vp, vp, sz]
+        L.msk144_push_interleaved.argtypes = [vp, vp, sz, C.c_int]
         L.msk144_poll.argtypes = [vp, C.POINTER(Line), sz, C.POINTER(sz)]
         L.msk144_reset_stream.argtypes = [vp]
         L.msk144_decode_host.argtypes = [vp, vp, sz, C.c_int, C.POINTER(Line), sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
@@ -228,8 +229,12 @@ class Decoder:
         return {k: getattr(t, k) for k, _ in StageTimes._fields_}
 
     # -- streaming -------------------------------------------------------------------------------
-    def push(self, data: bytes):
-        _check(lib().msk144_push(self._h, data, len(data)))
+    def push(self, data: bytes, nchan: int = 1):
+        """Raw stdin bytes of one channel, or (nchan > 1) of `nchan` channels interleaved per time step."""
+        if nchan > 1:
+            _check(lib().msk144_push_interleaved(self._h, data, len(data), nchan))
+        else:
+            _check(lib().msk144_push(self._h, data, len(data)))
 
     def poll(self, cap: int = 1024) -> List[dict]:
         lines = (Line * cap)()

@@ -34,6 +34,7 @@ static void show_help(const char* prog) {
     std::cout << "                   --device=0                  CUDA device ordinal." << std::endl;
     std::cout << "                   --batch-blocks=128          Blocks per GPU launch group when input arrives faster than real time." << std::endl;
     std::cout << "                   --per-payload-text          Decode every payload's own text (the reference reuses the first decode of a block)." << std::endl;
+    std::cout << "                   --channels=1                stdin carries N channels, one sample of each per time step; lines end with channel=<c>." << std::endl;
     std::cout << "                   --wav                       Skip a RIFF/WAVE header at the start of stdin (the reference decodes it as samples)." << std::endl;
     std::cout << "                   --json                      One JSON object per line instead of the '***' line format." << std::endl;
     std::cout << "                   --dedupe[=2]                One line per ping: merge the per-block repeats of a message at most N blocks apart." << std::endl;
@@ -53,6 +54,7 @@ int main(int argc, char* const argv[]) {
     cfg.flags = MSK144_FLAG_COMPAT_DECODE_CACHE;
     bool center_set = false, json = false;
     int dedupe_gap = -1;  // < 0: print every per-block line, as the reference does
+    int nchan = 1;
     static struct option long_options[] = {{"help", no_argument, 0, 0},                     // 0
                                            {"center-frequency", required_argument, 0, 0},   // 1
                                            {"search-step", required_argument, 0, 0},        // 2
@@ -68,6 +70,7 @@ int main(int argc, char* const argv[]) {
                                            {"json", no_argument, 0, 0},                     // 12
                                            {"dedupe", optional_argument, 0, 0},             // 13
                                            {"unpack77-lib", required_argument, 0, 0},       // 14
+                                           {"channels", required_argument, 0, 0},           // 15
                                            {0, 0, 0, 0}};
     while (true) {
         int option_index = 0;
@@ -95,6 +98,7 @@ int main(int argc, char* const argv[]) {
                     return 2;
                 }
                 break;
+            case 15: nchan = atoi(optarg) > 0 ? atoi(optarg) : 1; break;
             default: show_help(argv[0]); return 0;
         }
     }
@@ -129,8 +133,8 @@ int main(int argc, char* const argv[]) {
               << "GPU SMs: " << info.sm_count << std::endl
               << std::endl;
 
-    const size_t hop_bytes = MSK144_HOP_SAMPLES * 2;  // both modes: 2 bytes per sample
-    const size_t block_bytes = MSK144_BLOCK_SAMPLES * 2;
+    const size_t hop_bytes = MSK144_HOP_SAMPLES * 2 * static_cast<size_t>(nchan);  // both modes: 2 bytes per sample
+    const size_t block_bytes = MSK144_BLOCK_SAMPLES * 2 * static_cast<size_t>(nchan);
     std::vector<unsigned char> buf(hop_bytes * static_cast<size_t>(cfg.max_batch_blocks > 0 ? cfg.max_batch_blocks : 128));
     std::vector<msk144_line> lines(4096);
     size_t total_bytes = 0;
@@ -143,7 +147,8 @@ int main(int argc, char* const argv[]) {
         char out[512];
         if (json) msk144_format_line_json(&l, nullptr, out, sizeof(out));
         else msk144_format_line(&l, nullptr, out, sizeof(out));
-        std::cout << out << std::endl;
+        if (!json && nchan > 1) std::cout << out << "channel=" << l.channel << "; " << std::endl;
+        else std::cout << out << std::endl;
     };
     auto drain_events = [&](int flush) {
         size_t ne = 0;
@@ -166,7 +171,9 @@ int main(int argc, char* const argv[]) {
         const auto t0 = std::chrono::steady_clock::now();
         const int64_t before = 0;
         (void)before;
-        if (msk144_push(dec, buf.data(), static_cast<size_t>(n)) != MSK144_OK) {
+        const int prc = nchan > 1 ? msk144_push_interleaved(dec, buf.data(), static_cast<size_t>(n), nchan)
+                                  : msk144_push(dec, buf.data(), static_cast<size_t>(n));
+        if (prc != MSK144_OK) {
             std::cerr << msk144_last_error() << std::endl;
             rc_exit = 2;
             break;

@@ -158,6 +158,11 @@ struct msk144_decoder {
     // streaming state (msk144_push / msk144_poll)
     std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
     int share_twins = std::getenv("MSK144_NO_TWINS") ? 0 : 1;  // A/B knob; results are identical either way
+    // multi-channel streaming state (msk144_push_interleaved): raw interleaved bytes, one SNR recurrence per channel
+    int il_nchan = 0;
+    std::vector<uint8_t> il_pending;
+    std::vector<mskhost::SnrTracker> il_snr;
+    int64_t il_next_block = 0;
     bool wav_checked = false;      // MSK144_FLAG_SKIP_WAV_HEADER: the start of the stream has been examined
     int64_t next_block = 0;
     mskhost::SnrTracker stream_snr;
@@ -408,8 +413,8 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
         for (int64_t gb = g0; gb < g0 + nb; gb++) {
             const int ch = static_cast<int>(gb / bpc);
             const int64_t k = gb % bpc;
-            if (k == 0) local = mskhost::SnrTracker();  // every channel starts a fresh SNR recurrence
-            mskhost::SnrTracker* snr = (carry && nchan == 1) ? carry : &local;
+            if (k == 0) local = mskhost::SnrTracker();  // every channel starts a fresh SNR recurrence ...
+            mskhost::SnrTracker* snr = carry ? &carry[ch] : &local;  // ... unless the caller carries one per channel
             snr->process_powers(&powers[static_cast<size_t>(gb - g0) * 8]);
             std::vector<mskhost::Present> present;
             while (ri < raw.size() && raw[ri].gblock == gb) {
@@ -731,6 +736,7 @@ int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, in
 int msk144_reset_stream(msk144_decoder* dec) {
     if (!dec) return fail(MSK144_EINVAL, "null argument");
     dec->pending.clear();
+    dec->il_pending.clear(), dec->il_snr.clear(), dec->il_nchan = 0, dec->il_next_block = 0;
     dec->wav_checked = false;
     dec->next_block = 0;
     dec->stream_snr.reset();
@@ -766,6 +772,38 @@ int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
     dec->next_block += static_cast<int64_t>(nblocks);
     // keep the second half of the last block: it is the first half of the next one (main.cu:284-288)
     dec->pending.erase(dec->pending.begin(), dec->pending.begin() + nblocks * (N / 2) * 2);
+    return MSK144_OK;
+}
+
+int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbytes, int nchan) {
+    if (!dec || (!bytes && nbytes) || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
+    if (dec->il_nchan == 0) {
+        dec->il_nchan = nchan;
+        dec->il_snr.assign(static_cast<size_t>(nchan), mskhost::SnrTracker());
+    } else if (dec->il_nchan != nchan) {
+        return fail(MSK144_EINVAL, "channel count changed in mid-stream (msk144_reset_stream first)");
+    }
+    CK(cudaSetDevice(dec->cfg.device));
+    const uint8_t* b = static_cast<const uint8_t*>(bytes);
+    dec->il_pending.insert(dec->il_pending.end(), b, b + nbytes);
+    const size_t frame = 2 * static_cast<size_t>(nchan);  // one time step of every channel
+    const size_t nsteps = dec->il_pending.size() / frame;
+    if (nsteps < static_cast<size_t>(N)) return MSK144_OK;
+    const size_t nblocks = (nsteps - N) / (N / 2) + 1;
+    const size_t used = (nblocks - 1) * (N / 2) + N;
+    const size_t ubytes = used * frame;
+    if (int rc = dec->ensure_raw(2 * ubytes + 16)) return rc;
+    char* d_cm = static_cast<char*>(dec->d_raw);
+    char* d_il = d_cm + ((ubytes + 15) / 16) * 16;
+    CK(cudaMemcpyAsync(d_il, dec->il_pending.data(), ubytes, cudaMemcpyHostToDevice, dec->stream));
+    dec->h2d_bytes += ubytes;
+    if (int rc = msk144_deinterleave_device(dec, d_il, d_cm, used, nchan, dec->stream)) return rc;
+    std::vector<msk144_line> lv;
+    if (int rc = dec->decode_common(d_cm, used, nchan, dec->stream, dec->il_next_block, dec->il_snr.data(), &lv, nullptr))
+        return rc;
+    for (const auto& l : lv) dec->out_lines.push_back(l);
+    dec->il_next_block += static_cast<int64_t>(nblocks);
+    dec->il_pending.erase(dec->il_pending.begin(), dec->il_pending.begin() + nblocks * (N / 2) * frame);
     return MSK144_OK;
 }
 

@@ -297,3 +297,35 @@ def test_interleaved_input_equals_channel_major(gpu, synth):
         b, rb = d.decode_host(il, nchan=5, interleaved=True)
     assert len(a) > 0 and a == b
     assert np.array_equal(ra, rb)
+
+
+def test_multichannel_streaming_equals_single_channel_streams(gpu, synth):
+    """msk144_push_interleaved: N channels interleaved per time step, ragged pushes; every channel's lines (snr
+    included: one recurrence per channel is carried) equal that channel pushed alone.  CLI --channels likewise."""
+    nch = 4
+    chans = [synth.cfg5_channel(c, seconds=6.0)[0] for c in range(nch)]
+    il = np.stack(chans, axis=1).copy().tobytes()
+    kw = dict(width=100, step=2, depth=3, thr=2)
+    want = []
+    for c in range(nch):
+        with gpu.Decoder(**kw) as d:
+            d.push(chans[c].tobytes())
+            want += [dict(l, channel=c) for l in d.poll(4096)]
+    with gpu.Decoder(**kw) as d:
+        got, i, rng = [], 0, np.random.default_rng(1)
+        while i < len(il):
+            n = int(rng.integers(1, 60000))
+            d.push(il[i:i + n], nchan=nch)
+            got += d.poll(4096)
+            i += n
+        with pytest.raises(gpu.Msk144Error):
+            d.push(il[:64], nchan=nch + 1)               # the channel count is fixed in mid-stream
+    key = lambda ls: sorted((l["channel"],) + lines_key([l])[0] for l in ls)
+    assert len(want) > 0 and key(got) == key(want)
+    p = subprocess.run([gpu.CLI_PATH, "--search-width=100", "--scan-depth=3", "--nbadsync-threshold=2", f"--channels={nch}"],
+                       input=il, capture_output=True)
+    out = p.stdout.decode().splitlines()
+    assert p.returncode == 0 and out[-1] == "Done"
+    import re
+    cli = sorted((int(re.search(r"channel=(\d+); $", l).group(1)), re.search(r"msg='(.*)';", l).group(1)) for l in out[:-1])
+    assert cli == sorted((l["channel"], l["text"]) for l in want)
