@@ -8,6 +8,7 @@
 #include <getopt.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <chrono>
 #include <cstdio>
 #include <cstdlib>
@@ -135,7 +136,9 @@ int main(int argc, char* const argv[]) {
 
     const size_t hop_bytes = MSK144_HOP_SAMPLES * 2 * static_cast<size_t>(nchan);  // both modes: 2 bytes per sample
     const size_t block_bytes = MSK144_BLOCK_SAMPLES * 2 * static_cast<size_t>(nchan);
-    std::vector<unsigned char> buf(hop_bytes * static_cast<size_t>(cfg.max_batch_blocks > 0 ? cfg.max_batch_blocks : 128));
+    // one read = up to one launch group of blocks (counted over all channels)
+    const size_t group_blocks = static_cast<size_t>(cfg.max_batch_blocks > 0 ? cfg.max_batch_blocks : 128);
+    std::vector<unsigned char> buf(hop_bytes * std::max<size_t>(1, group_blocks / static_cast<size_t>(nchan)));
     std::vector<msk144_line> lines(4096);
     size_t total_bytes = 0;
     int rc_exit = 0;
