@@ -125,7 +125,7 @@ def run_reference(args, rank):
             note = ("unmodified reference CLI (its CUDA kernels recompiled for sm_100a, no fast-math) on the same B200; "
                     "wall clock of the whole process incl. CUDA context creation and cuFFT plan (~0.3 s)")
         except Exception as e:  # noqa: BLE001
-            usable, note = False, f"reference binary unusable ({str(e)[:120]}); CPU oracle port instead"
+            usable, note = False, f"reference binary unusable ({' '.join(str(e).split())[:120]}); CPU oracle port instead"
             times = []
     if not usable:
         from oracle import orc
@@ -145,7 +145,7 @@ def run_reference(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": f"first {sample_s:.0f} s of the stream = {nblocks} blocks per step"},
+            "config": {"workload": WORKLOAD, "sample": f"first {nblocks} blocks ({audio_s:.1f} s of audio) of the stream per step"},
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": f"{nblocks} blocks ({audio_s:.1f} s of audio) per step; {note}"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
