@@ -130,7 +130,7 @@ def run_reference(args, rank):
     if not usable:
         from oracle import orc
         kind, cores = "port", os.cpu_count() or 1
-        nb_s = min(nblocks, 8 * cores)
+        nb_s = min(nblocks, int(os.environ.get("MSK144_BENCH_REF_BLOCKS", 8 * cores)))  # env: contract tests only
         audio_s = nb_s * 0.216
         cfg = orc.config(center=1500.0, width=500.0, step=1.0, depth=6, thr=3, scan_mode=1, nthreads=cores)
         for i in range(min(1, args.warmup) + args.steps):
