@@ -10,16 +10,26 @@ One step = one pass of the whole hot path (front end -> scan/softbits/gate -> LD
 With N > 1 every rank decodes its own 15-minute stream (independent channels, no collective on the
 data path): weak scaling, value = total audio seconds / max-over-ranks device time.
 
-  value  audio seconds decoded per second, input resident in HBM, timed with CUDA events
-  e2e    same through msk144_decode_host: pinned host input, H2D + kernels + D2H + host text decode
-  roofline / cpu_baseline: see DESIGN.md
---impl reference runs the unmodified reference (oracle/_ref/msk144cudecoder_ref: its own CUDA kernels
-recompiled for sm_100a, its own CLI) on a bounded sample of the same stream; if that binary is not
-usable it falls back to the CPU oracle port on all host cores.
+  value     audio seconds decoded per second, input resident in HBM, timed with CUDA events
+  e2e       same through msk144_decode_host: pinned host input, H2D + kernels + D2H + host text decode
+  roofline  FP32-issue roof of the dominant kernel (the path is not HBM-bound); HBM as a sub-object
+  cli       the same stream through the drop-in executable (bytes on stdin, lines on stdout), start-up separated
+  cfg5      BASELINE.json configs[4]: 1024 channels x 60 s, sharded over the ranks by msk144cudecoder_b200.sharding,
+            host-side gather of the decode lines inside the timed region
+  cpu_baseline, lines_identical_to_reference: see DESIGN.md section 6
+
+--impl reference runs the UNMODIFIED reference (oracle/_ref/msk144cudecoder_ref: its own CUDA kernels recompiled
+for sm_100a, its own CLI; the reference has no CPU implementation of the path) on a bounded sample of the same
+stream -- the first 60 s -- once per step, plus one pass over the whole stream outside the step loop; its fixed
+process start-up is measured on a one-block input and reported.  If that binary is not usable the arm falls back
+to the CPU oracle port on all host cores.
 """
 import argparse
+import hashlib
 import json
+import multiprocessing as mp
 import os
+import re
 import subprocess
 import sys
 import threading
@@ -31,11 +41,25 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLAGS = dict(center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
+CLI_FLAGS = ["--search-step=1", "--search-width=500", "--scan-depth=6", "--nbadsync-threshold=3"]
 STREAM_SECONDS = 900.0
+SAMPLE_SECONDS = 60.0     # the reference arm's bounded sample: first 276 blocks == tests/golden/audio_deep_60s.npz
 METRIC = "real_time_factor_deep_scan"
 UNIT = "audio_s_per_s"
 WORKLOAD = ("cfg2: synthetic 15-min 12 kHz s16 audio, pings at SNR -4..+10 dB; --search-step=1 --search-width=500 "
             "--scan-depth=6 --nbadsync-threshold=3 (NF=501, 24048 candidates/block, 4165 blocks)")
+REF_EXE = os.path.join(ROOT, "oracle", "_ref", "msk144cudecoder_ref")
+GOLDEN_60S = os.path.join(ROOT, "tests", "golden", "audio_deep_60s.npz")
+
+
+def workload_config(world, seconds=STREAM_SECONDS):
+    """The `config` object: identical in both arms (it names the workload, not the implementation)."""
+    nblocks = (int(seconds * 12000) - 5184) // 2592 + 1
+    return {"workload": WORKLOAD if seconds == STREAM_SECONDS else WORKLOAD + f" [shortened to {seconds:.0f} s]",
+            "streams": world, "blocks_per_stream": nblocks, "flags": " ".join(CLI_FLAGS), "seed": 144,
+            "decode_cache_quirk": "reproduced (MSK144_FLAG_COMPAT_DECODE_CACHE: a block's first text is reused, main.cu:437-445)",
+            "l2": "ours: 256 MiB memset between steps, per-step intermediates (1.7 GB LLR queue) exceed L2; reference: one process per step",
+            "parallelism": f"{world} independent stream(s), one process per GPU, no data-path collective"}
 
 
 def peaks():
@@ -90,66 +114,143 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def algorithmic_flops(nf, depth, nblocks, ncw_iters):
-    """per-block work in the direct (reformulated, no early-out) form."""
+def algorithmic_flops(nf, depth, nblocks):
+    """per-block work of scan + soft bits in the direct (reformulated, no early-out) form."""
     scan = nf * (1_798_848 + 31_104 * depth)
     soft = nf * depth * 8 * 15_300
-    return nblocks * (scan + soft), ncw_iters * 6_200, nblocks * scan, nblocks * soft
+    return nblocks * scan, nblocks * soft
 
 
+# ---------------------------------------------------------------------------------------- CLI harness (both arms)
+def mask_date(text):
+    return [re.sub(r"date=\d{14}", "date=" + "x" * 14, l) for l in text.splitlines()]
+
+
+def cli_once(cmd, data, timeout=1800):
+    """One process: bytes on stdin, stdout captured.  Returns (wall seconds, masked stdout lines)."""
+    env = dict(os.environ, LD_LIBRARY_PATH="/usr/local/cuda/lib64:" + os.environ.get("LD_LIBRARY_PATH", ""))
+    t0 = time.perf_counter()
+    p = subprocess.run(cmd, input=data, capture_output=True, env=env, timeout=timeout)
+    dt = time.perf_counter() - t0
+    out = p.stdout.decode(errors="replace")
+    if p.returncode != 0 or not out.rstrip().endswith("Done"):
+        raise RuntimeError(f"rc={p.returncode}: " + p.stderr.decode(errors="replace")[-300:])
+    return dt, mask_date(out)
+
+
+def cli_figures(cmd, sample, full, steps, warmup, audio_s_sample, audio_s_full):
+    """Wall-clock figures of a stdin->stdout executable: fixed start-up on a one-block input, the 60 s sample per
+    step (median), one pass over the whole stream.  Steady-state = start-up subtracted."""
+    one_block = sample[: 5184 * 2]
+    startup = float(np.median([cli_once(cmd, one_block)[0] for _ in range(3)]))
+    times, lines = [], None
+    for i in range(warmup + steps):
+        dt, ls = cli_once(cmd, sample)
+        if lines is not None and ls != lines:
+            raise RuntimeError("output differs between two runs on the same input")
+        lines = ls
+        if i >= warmup:
+            times.append(dt)
+    dt_med = float(np.median(times))
+    out = {"startup_s": startup, "sample_s_median": dt_med, "sample_s_all": [round(t, 4) for t in times],
+           "raw_value": audio_s_sample / dt_med, "value": audio_s_sample / max(1e-9, dt_med - startup), "unit": UNIT,
+           "sample": f"first {int(round(audio_s_sample / 0.216))} blocks ({audio_s_sample:.1f} s of audio) per process, "
+                     "bytes on stdin, lines on stdout; value = steady state (start-up on a one-block input subtracted), "
+                     "raw_value = whole process wall clock"}
+    if full is not None:
+        dt_full, full_lines = cli_once(cmd, full)
+        out.update(full_stream_s=dt_full, full_stream_raw_value=audio_s_full / dt_full,
+                   full_stream_value=audio_s_full / max(1e-9, dt_full - startup), full_stream_lines=len(full_lines) - 1)
+    return out, lines
+
+
+def lines_digest(lines):
+    return hashlib.sha256("\n".join(lines).encode()).hexdigest()[:16]
+
+
+def golden_lines():
+    if os.path.exists(GOLDEN_60S):
+        return [str(s) for s in np.load(GOLDEN_60S)["cli_lines"]]
+    return None
+
+
+def cfg2_stream(seed=144, seconds=STREAM_SECONDS):
+    from msk144cudecoder_b200 import synth
+    return synth.cfg2_deep_audio(seconds=seconds, seed=seed)
+
+
+# ---------------------------------------------------------------------------------------- reference arm
 def run_reference(args, rank):
-    """The reference arm: unmodified reference binary over its own CLI, bounded sample of the workload."""
+    """The reference arm: unmodified reference binary over its own CLI, bounded sample of the workload per step."""
     if rank != 0:
         return
     from msk144cudecoder_b200 import synth
-    sample_s = 60.0
-    x, _ = synth.cfg2_deep_audio(seconds=STREAM_SECONDS, seed=144)
-    x = np.ascontiguousarray(x[: int(sample_s * 12000)])
-    nblocks = synth.num_blocks(len(x))
+    x, _ = cfg2_stream(seconds=args.seconds)
+    ns = int(min(SAMPLE_SECONDS, args.seconds) * 12000)
+    sample = np.ascontiguousarray(x[:ns])
+    nblocks = synth.num_blocks(len(sample))
     audio_s = nblocks * 0.216
-    exe = os.path.join(ROOT, "oracle", "_ref", "msk144cudecoder_ref")
-    env = dict(os.environ, LD_LIBRARY_PATH="/usr/local/cuda/lib64:" + os.environ.get("LD_LIBRARY_PATH", ""))
-    cmd = [exe, "--search-step=1", "--search-width=500", "--scan-depth=6", "--nbadsync-threshold=3"]
-    kind, cores, times, note = "reference", 1, [], ""
-    usable = os.path.exists(exe)
+    audio_full = synth.num_blocks(len(x)) * 0.216
+    kind, cores, note, extra = "reference", 1, "", {}
+    usable = os.path.exists(REF_EXE)
     if usable:
         try:
-            for i in range(args.warmup + args.steps):
-                t0 = time.perf_counter()
-                p = subprocess.run(cmd, input=x.tobytes(), capture_output=True, env=env, timeout=900)
-                dt = time.perf_counter() - t0
-                if p.returncode != 0 or not p.stdout.decode(errors="replace").rstrip().endswith("Done"):
-                    raise RuntimeError(p.stderr.decode(errors="replace")[-300:])
-                if i >= args.warmup:
-                    times.append(dt)
-            note = ("unmodified reference CLI (its CUDA kernels recompiled for sm_100a, no fast-math) on the same B200; "
-                    "wall clock of the whole process incl. CUDA context creation and cuFFT plan (~0.3 s)")
+            fig, lines = cli_figures([REF_EXE] + CLI_FLAGS, sample.tobytes(), None if args.no_full_stream else x.tobytes(),
+                                     args.steps, args.warmup, audio_s, audio_full)
+            val, dt = fig["value"], fig["sample_s_median"]
+            gl = golden_lines()
+            extra = {"cli": fig, "raw_value": fig["raw_value"], "startup_s": fig["startup_s"],
+                     "full_stream_value": fig.get("full_stream_value"),
+                     "lines_sha16": lines_digest(lines), "lines": len(lines) - 1,
+                     "lines_identical_to_golden": (lines == gl) if gl is not None and args.seconds >= SAMPLE_SECONDS else None}
+            note = ("unmodified reference CLI (its CUDA kernels recompiled for sm_100a, no fast-math) on the same B200; one process "
+                    "per step, median; value = steady state: the process start-up (CUDA context, cuFFT plan; measured on a one-block "
+                    f"input: {fig['startup_s']:.2f} s) is subtracted, raw_value keeps it")
         except Exception as e:  # noqa: BLE001
             usable, note = False, f"reference binary unusable ({' '.join(str(e).split())[:120]}); CPU oracle port instead"
-            times = []
     if not usable:
         from oracle import orc
         kind, cores = "port", os.cpu_count() or 1
         nb_s = min(nblocks, int(os.environ.get("MSK144_BENCH_REF_BLOCKS", 8 * cores)))  # env: contract tests only
         audio_s = nb_s * 0.216
         cfg = orc.config(center=1500.0, width=500.0, step=1.0, depth=6, thr=3, scan_mode=1, nthreads=cores)
+        times = []
         for i in range(min(1, args.warmup) + args.steps):
             t0 = time.perf_counter()
-            orc.decode_stream(x, cfg, max_blocks=nb_s)
+            orc.decode_stream(sample, cfg, max_blocks=nb_s)
             if i >= min(1, args.warmup):
                 times.append(time.perf_counter() - t0)
         nblocks = nb_s
+        dt = float(np.median(times))
+        val = audio_s / dt
         note = note or "CPU oracle port (C++ restatement of the reference), all host cores"
-    dt = float(np.mean(times))
-    val = audio_s / dt
     line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": WORKLOAD, "sample": f"first {nblocks} blocks ({audio_s:.1f} s of audio) of the stream per step"},
+            "config": workload_config(args.gpus, args.seconds),
+            "reference_sample": f"first {nblocks} blocks ({audio_s:.1f} s of audio) of the stream per step",
             "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": f"{nblocks} blocks ({audio_s:.1f} s of audio) per step; {note}"},
             "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    line.update(extra)
     print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------- cfg5 input (before CUDA)
+def _cfg5_one(c):
+    from msk144cudecoder_b200 import synth
+    return synth.cfg5_channel(c, seconds=60.0)[0]
+
+
+def cfg5_input(channels, world):
+    """This rank's channels, synthesised on host cores in a fork pool (call before CUDA is initialised)."""
+    if not channels:
+        return np.zeros((0, 720000), np.int16)
+    workers = max(1, min(16, (os.cpu_count() or 1) // max(1, world)))
+    if workers == 1:
+        return np.stack([_cfg5_one(c) for c in channels])
+    with mp.get_context("fork").Pool(workers) as pool:
+        return np.stack(pool.map(_cfg5_one, channels, chunksize=4))
 
 
 def main():
@@ -162,6 +263,9 @@ def main():
     ap.add_argument("--batch-blocks", type=int, default=128)
     ap.add_argument("--cpu-blocks", type=int, default=0, help="blocks of the CPU baseline sample (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-full-stream", action="store_true", help="skip the one whole-stream pass of the CLI legs")
+    ap.add_argument("--no-cli", action="store_true", help="skip the CLI / reference-check legs of our arm")
+    ap.add_argument("--cfg5-channels", type=int, default=1024, help="channels of the multi-channel leg (0 = skip)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -171,11 +275,17 @@ def main():
         run_reference(args, rank)
         return
 
+    from msk144cudecoder_b200 import sharding, synth
+
+    # ---- host-side synthesis first (fork pool: before CUDA exists in this process) ---------------------
+    x, pings = cfg2_stream(seed=144 + rank, seconds=args.seconds)
+    my_chans = sharding.channels_of_rank(args.cfg5_channels, rank, world) if args.cfg5_channels > 0 else []
+    x5 = cfg5_input(my_chans, world) if args.cfg5_channels > 0 else None
+
     import torch
     import torch.distributed as dist
 
     import msk144cudecoder_b200 as m
-    from msk144cudecoder_b200 import synth
 
     assert torch.cuda.is_available(), "bench.py needs a GPU: the decoder has no CPU path"
     torch.cuda.set_device(local_rank)
@@ -184,14 +294,13 @@ def main():
         dist.init_process_group("nccl", device_id=dev)
 
     # ---- workload: one 15-min stream per rank (rank r = channel r) ------------------------------------
-    x, pings = synth.cfg2_deep_audio(seconds=args.seconds, seed=144 + rank)
     nsamp = len(x)
     nblocks = synth.num_blocks(nsamp)
     audio_s = nblocks * 0.216   # every block advances the stream by one 2592-sample hop
     x_pinned = torch.from_numpy(x).pin_memory()
     x_dev = x_pinned.to(dev, non_blocking=True)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
-    dec = m.Decoder(device=local_rank, max_batch_blocks=args.batch_blocks, **FLAGS)
+    dec = m.Decoder(device=local_rank, max_batch_blocks=args.batch_blocks, compat_cache=True, **FLAGS)
     stream = torch.cuda.Stream(dev)   # the kernels are launched on this stream; the events below are recorded on it
     torch.cuda.synchronize(dev)
 
@@ -211,7 +320,6 @@ def main():
         device_step()
     barrier()
     dec.stage_times()   # drop warm-up timings
-    l0 = None
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local_rank) as clk:
         ev0.record(stream)
@@ -248,54 +356,109 @@ def main():
     found_texts = {l["text"] for l in lines}
     sent_texts = {p.text for p in pings}
 
+    # ---- cfg5: 1024 channels x 60 s over all ranks, host-side gather of the lines inside the timed region ----
+    cfg5 = None
+    if args.cfg5_channels > 0:
+        x5p = torch.from_numpy(x5).pin_memory() if len(my_chans) else None
+
+        def cfg5_pass():
+            def decode_channels(chans):
+                return dec.decode_host(x5p.numpy(), nchan=len(chans), line_cap=1 << 17, result_cap=0)[0]
+            t_a = time.perf_counter()
+            mine = [dict(l, channel=my_chans[l["channel"]]) for l in decode_channels(my_chans)] if my_chans else []
+            t_b = time.perf_counter()
+            merged = sharding.gather_lines(mine, rank, world)
+            return merged, t_b - t_a, time.perf_counter() - t_b
+
+        cfg5_pass()                       # warm-up (buffers grow to the multi-channel shape)
+        barrier()
+        dec.stage_times()
+        t0 = time.perf_counter()
+        merged, t_dec, t_gather = cfg5_pass()
+        barrier()
+        t_pass = time.perf_counter() - t0
+        s5 = dec.stage_times()
+        tt = torch.tensor([t_pass, t_dec, t_gather], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        t_pass, t_dec, t_gather = (float(v) for v in tt.tolist())
+        if rank == 0:
+            key = hashlib.sha256(repr([(l["channel"], l["block"], l["text"], l["num_avg"], l["nbadsync"], l["snr"])
+                                       for l in merged]).encode()).hexdigest()[:16]
+            cfg5 = {"workload": f"cfg5: {args.cfg5_channels} independent synthetic 12 kHz channels x 60 s (seed 1000 + c, 20 pings each), deep-scan flags",
+                    "sharding": f"contiguous channel ranges over {world} rank(s) (msk144cudecoder_b200.sharding), one decode_host call per rank "
+                                "(pinned host samples in), gather_object of the decode lines to rank 0 + ordered merge, all inside the timed pass",
+                    "channels": args.cfg5_channels, "seconds_per_channel": 60.0, "pass_s": t_pass, "decode_s_max_rank": t_dec,
+                    "gather_merge_s": t_gather, "realtime_channels": args.cfg5_channels * 60.0 / t_pass,
+                    "audio_s_per_s": args.cfg5_channels * 276 * 0.216 / t_pass, "merged_lines": len(merged), "merged_lines_sha16": key,
+                    "rank0_kernel_ms": {"frontend": s5["frontend_ms"], "scan": s5["scan_ms"], "ldpc": s5["ldpc_ms"]},
+                    "timing": "wall clock between barriers, max over ranks (includes host text decode and the gather); 1 warm-up + 1 timed pass"}
+        del x5p
+
     if rank == 0:
         hbm_peak, sm_mhz, peak_src = peaks()
         # dominant kernel by measured device time over the timed region
         per = {"frontend_kernel": st["frontend_ms"], "scan_kernel": st["scan_ms"], "ldpc_kernel": st["ldpc_ms"]}
         dom = max(per, key=per.get)
         groups = max(1, st["groups"])
+        launches_per_step = max(1, groups // args.steps)
         ncw = b1["llr_codewords"]          # gated candidates of one pass over the stream (last e2e pass)
         nsucc = b1["ldpc_successes"]
-        scan_soft_flops, ldpc_flops_max, scan_flops, soft_flops = algorithmic_flops(dec.num_freqs, dec.depth, nblocks, ncw * 10)
-        fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+        scan_flops, soft_flops = algorithmic_flops(dec.num_freqs, dec.depth, nblocks)
+        # LDPC work actually executed: a codeword that does not converge runs 10 parity checks and the 9 message
+        # updates between them; the (few) successes stop earlier and are not credited at all
+        ldpc_updates = max(0, ncw - nsucc) * 9
+        fp32_nominal = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
+        try:
+            fp32_meas = dec.measure_fp32_peak()
+        except Exception:  # noqa: BLE001
+            fp32_meas = None
         dur = {k: v / 1e3 / args.steps for k, v in per.items()}   # seconds per pass
-        # algorithmic bytes per pass of each kernel
+        # algorithmic work and bytes per pass of each kernel
+        flops_alg = {"frontend_kernel": nblocks * 5184 * (26 * 4 + 12), "scan_kernel": scan_flops + soft_flops,
+                     "ldpc_kernel": ldpc_updates * 6_200}
         bytes_alg = {"frontend_kernel": nblocks * (5184 * 2 + 5184 * 8 + 32),
                      "scan_kernel": nblocks * (5184 * 8 + dec.items_per_block * 16) + ncw * 544,
                      "ldpc_kernel": ncw * 544 + nsucc * 48}
-        flops_alg = {"frontend_kernel": nblocks * 5184 * (26 * 4 + 12), "scan_kernel": scan_soft_flops,
-                     "ldpc_kernel": ldpc_flops_max}
-        ach_gbs = bytes_alg[dom] / dur[dom] / 1e9
-        ach_tf = flops_alg[dom] / dur[dom] / 1e12
+        ach_tf = {k: flops_alg[k] / dur[k] / 1e12 if dur[k] > 0 else 0.0 for k in per}
+        ach_gbs = {k: bytes_alg[k] / dur[k] / 1e9 if dur[k] > 0 else 0.0 for k in per}
+        peak_tf = fp32_meas or fp32_nominal
         # dram__bytes_read + dram__bytes_write of the dominant kernel from the committed `ncu --set full` capture
         # (one 128-block launch group of this workload), scaled to this run's average launch
         traffic, ncu_pipes = None, None
         try:
             tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-            traffic = tj["dram_bytes_per_launch"][dom] * (nblocks / max(1, groups // args.steps)) / tj["blocks_per_launch"]
+            traffic = tj["dram_bytes_per_launch"][dom] * (nblocks / launches_per_step) / tj["blocks_per_launch"]
             ncu_pipes = {"issue_active_pct": tj.get("issue_active_pct", {}).get(dom), **tj.get("pipe_pct", {}).get(dom, {}),
                          "source": tj.get("source")}
         except Exception:  # noqa: BLE001
             pass
-        roofline = {"bound": "hbm", "kernel": dom, "achieved": ach_gbs, "peak": hbm_peak, "unit": "GB/s",
-                    "frac": ach_gbs / hbm_peak, "traffic": traffic, "algorithmic_bytes_per_launch": bytes_alg[dom] / max(1, groups // args.steps),
-                    "traffic_source": "profiles/ncu_traffic.json", "peak_source": peak_src,
-                    "launches_per_step": groups // args.steps, "avg_launch_ms": per[dom] / groups,
-                    "binding": "instruction issue of a packed-FP32 / ALU / MUFU mix (not HBM: algorithmic HBM traffic is ~0.5 KB per codeword / "
-                               "41 KB per block); ldpc_kernel issues 0.625 warp instructions per cycle per scheduler against 0.73-0.78 "
-                               "measured for a dependency-free stream of the same mix (profiles/r01_v6_pipes.txt)",
-                    "fp32": {"achieved": ach_tf, "peak": fp32_peak, "unit": "TFLOP/s", "frac": ach_tf / fp32_peak,
-                             "peak_source": f"148 SM x 128 lanes x 2 x {sm_mhz:.0f} MHz"},
-                    "ncu_pipes_pct_of_peak": ncu_pipes,
-                    "kernel_share_of_step": {k: v / max(1e-9, st["total_ms"]) for k, v in per.items()},
-                    "kernel_ms_per_step": {k: v / args.steps for k, v in per.items()}}
+        whole_tf = sum(flops_alg.values()) / (st["total_ms"] / 1e3 / args.steps) / 1e12
+        roofline = {"bound": "fp32", "kernel": dom, "achieved": ach_tf[dom], "peak": peak_tf, "unit": "TFLOP/s",
+                    "frac": ach_tf[dom] / peak_tf, "traffic": traffic,
+                    "work": ("ldpc_kernel: (codewords - successes) x 9 message updates executed x 6,200 flop (SURVEY.md 8d), "
+                             f"= {ldpc_updates} updates per step; scan_kernel: 8d's direct form per block"),
+                    "peak_source": ("measured on this GPU by msk144_measure_fp32_peak (dependency-free FFMA stream, CUDA events)"
+                                    if fp32_meas else "nominal (probe failed)"),
+                    "peak_nominal": fp32_nominal, "peak_nominal_source": f"148 SM x 128 lanes x 2 x {sm_mhz:.0f} MHz",
+                    "frac_of_nominal": ach_tf[dom] / fp32_nominal,
+                    "launches_per_step": launches_per_step, "avg_launch_ms": per[dom] / groups,
+                    "algorithmic_flop_per_launch": flops_alg[dom] / launches_per_step,
+                    "hbm": {"achieved": ach_gbs[dom], "peak": hbm_peak, "unit": "GB/s", "frac": ach_gbs[dom] / hbm_peak,
+                            "algorithmic_bytes_per_launch": bytes_alg[dom] / launches_per_step, "traffic": traffic,
+                            "traffic_source": "profiles/ncu_traffic.json", "peak_source": peak_src},
+                    "per_kernel": {k: {"ms_per_step": per[k] / args.steps, "share_of_step": per[k] / max(1e-9, st["total_ms"]),
+                                       "fp32_tflops": ach_tf[k], "fp32_frac": ach_tf[k] / peak_tf,
+                                       "hbm_gbs": ach_gbs[k], "hbm_frac": ach_gbs[k] / hbm_peak} for k in per},
+                    "whole_step": {"fp32_tflops": whole_tf, "fp32_frac": whole_tf / peak_tf},
+                    "binding": "instruction issue of a packed-FP32 / ALU / MUFU mix (not HBM: algorithmic HBM traffic is ~0.5 KB per "
+                               "codeword / 41 KB per block); see DESIGN.md section 4 and profiles/",
+                    "ncu_pipes_pct_of_peak": ncu_pipes}
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
                 "warmup": args.warmup, "ms_per_step": ms_max / args.steps, "higher_is_better": True, "scaling": "weak",
                 "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": WORKLOAD if args.seconds == STREAM_SECONDS else WORKLOAD + f" [shortened to {args.seconds:.0f} s]",
-                           "streams": world, "blocks_per_stream": nblocks, "batch_blocks": args.batch_blocks,
-                           "l2": "256 MiB memset between steps; per-step intermediates (1.7 GB LLR queue) exceed L2",
-                           "parallelism": f"{world} independent stream(s), one process per GPU, no data-path collective"},
+                "config": workload_config(world, args.seconds),
+                "batch_blocks": args.batch_blocks, "build": m.build_info(),
                 "clocks": clk.summary(),
                 "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                         "decode_lines_per_step": len(lines), "messages_found": len(found_texts & sent_texts),
@@ -304,7 +467,35 @@ def main():
                 "ldpc_codewords_per_s": ncw / dur["ldpc_kernel"] if dur["ldpc_kernel"] > 0 else None,
                 "ldpc_codewords_per_step": int(ncw),
                 "roofline": roofline}
-        if not args.no_cpu_baseline:
+        if cfg5 is not None:
+            line["cfg5"] = cfg5
+        if world == 1 and not args.no_cli:
+            # ---- the drop-in executable on the same bytes, and its output against the reference's ----------
+            try:
+                ns = int(min(SAMPLE_SECONDS, args.seconds) * 12000)
+                sample = np.ascontiguousarray(x[:ns]).tobytes()
+                fig, cli_lines = cli_figures([m.CLI_PATH, f"--device={local_rank}"] + CLI_FLAGS, sample,
+                                             None if args.no_full_stream else x.tobytes(), min(args.steps, 5), 1,
+                                             synth.num_blocks(ns) * 0.216, audio_s)
+                line["cli"] = fig
+                check = {"sample": f"first {synth.num_blocks(ns)} blocks of the stream through both executables, stdout compared "
+                                   "line by line (date masked)", "ours_lines": len(cli_lines) - 1, "ours_sha16": lines_digest(cli_lines)}
+                gl = golden_lines()
+                if gl is not None and args.seconds >= SAMPLE_SECONDS:
+                    check["golden"] = cli_lines == gl          # committed output of the reference (tests/golden)
+                if os.path.exists(REF_EXE):
+                    try:
+                        _, ref_lines = cli_once([REF_EXE] + CLI_FLAGS, sample)   # the checker, outside every timed region
+                        check["live"] = cli_lines == ref_lines
+                        check["reference_lines"], check["reference_sha16"] = len(ref_lines) - 1, lines_digest(ref_lines)
+                    except Exception as e:  # noqa: BLE001
+                        check["live_error"] = " ".join(str(e).split())[:160]
+                verdicts = [check[k] for k in ("golden", "live") if k in check]
+                line["lines_identical_to_reference"] = all(verdicts) if verdicts else None
+                line["reference_check"] = check
+            except Exception as e:  # noqa: BLE001
+                line["cli"] = {"error": " ".join(str(e).split())[:200]}
+        if world == 1 and not args.no_cpu_baseline:
             from oracle import orc
             cores = os.cpu_count() or 1
             nb_s = args.cpu_blocks or max(1, min(nblocks, 8 * cores))
@@ -322,6 +513,7 @@ def main():
         print(json.dumps(line), flush=True)
     dec.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 

@@ -62,7 +62,7 @@ typedef struct msk144_config {
     int32_t analytic_method;   /* --analytic-method: 1 = FFT, 2 = shift/LPF/shift (audio only) */
     int32_t nbadsync_threshold; /* --nbadsync-threshold, 1 */
     int32_t device;            /* CUDA device ordinal */
-    int32_t max_batch_blocks;  /* blocks per launch group (0 = default 256) */
+    int32_t max_batch_blocks;  /* blocks per launch group (0 = default 128) */
     int32_t flags;             /* MSK144_FLAG_* */
     int32_t reserved[6];
 } msk144_config;
@@ -247,6 +247,37 @@ int msk144_aggregator_add(msk144_aggregator* agg, const msk144_line* lines, size
  * stream will produce), or all of them if flush != 0 */
 int msk144_aggregator_poll(msk144_aggregator* agg, int64_t next_block, int flush, msk144_event* out, size_t cap,
                            size_t* nout);
+
+/* ---- several GPUs of one box (channels are independent, no exchange step) -------------
+ * The reference is one process, one GPU, one channel (main.cu:98-115,261-298).  A pool owns one decoder per listed
+ * device; channels are split into contiguous, balanced ranges (the first nchan % ndevices members get one more),
+ * every member runs on its own host thread with its own CUDA streams, and the decode lines are merged on the host.
+ * Output (content and order) equals what a single decoder returns for the same input.  A device may be listed more
+ * than once (two decoders sharing a GPU).  Errors: msk144_pool_last_error() for the calling thread. */
+typedef struct msk144_pool msk144_pool;
+const char* msk144_pool_last_error(void);
+int msk144_pool_create(const msk144_config* cfg, const int32_t* devices, int32_t ndevices, msk144_pool** out);
+void msk144_pool_destroy(msk144_pool* pool);
+int msk144_pool_size(const msk144_pool* pool);
+msk144_decoder* msk144_pool_member(msk144_pool* pool, int32_t i); /* for msk144_get_stage_times etc. */
+/* == msk144_decode_host over all members */
+int msk144_pool_decode_host(msk144_pool* pool, const void* samples, size_t samples_per_channel, int nchan,
+                            msk144_line* lines, size_t line_cap, size_t* nlines,
+                            msk144_result* results, size_t result_cap, size_t* nresults);
+/* == msk144_push_interleaved / msk144_poll / msk144_reset_stream over all members; nbytes must be a whole number of
+ * time steps (2 * nchan bytes each) */
+int msk144_pool_push_interleaved(msk144_pool* pool, const void* bytes, size_t nbytes, int nchan);
+int msk144_pool_poll(msk144_pool* pool, msk144_line* lines, size_t cap, size_t* nlines);
+int msk144_pool_reset_stream(msk144_pool* pool);
+
+/* ---- measurement helpers -------------------------------------------------------------------------------------- */
+/* Sustained FP32 FMA rate of the decoder's device: a dependency-free FFMA stream (8 independent chains per thread,
+ * every SM sub-partition saturated), timed with CUDA events; *tflops = 2 * FMAs / time.  This is the measured
+ * denominator of bench.py's FP32 roofline (MEASURED_PEAKS.json has no FP32 number). */
+int msk144_measure_fp32_peak(msk144_decoder* dec, double* tflops);
+/* "nvcc <major>.<minor>.<build>; sm_100a; <date>": the LDPC kernel's tanh reproduces libdevice of this toolkit
+ * (msk144_selftest_ldpc_math checks it on the device). */
+const char* msk144_build_info(void);
 
 #ifdef __cplusplus
 }

@@ -33,6 +33,9 @@ EXPORTED_SYMBOLS = [
     "msk144_set_unpack77_library", "msk144_unpack77_is_external", "msk144_wav_data_offset", "msk144_format_line_json",
     "msk144_deinterleave_device", "msk144_decode_host_interleaved", "msk144_push_interleaved",
     "msk144_aggregator_create", "msk144_aggregator_destroy", "msk144_aggregator_add", "msk144_aggregator_poll",
+    "msk144_pool_last_error", "msk144_pool_create", "msk144_pool_destroy", "msk144_pool_size", "msk144_pool_member",
+    "msk144_pool_decode_host", "msk144_pool_push_interleaved", "msk144_pool_poll", "msk144_pool_reset_stream",
+    "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math",
 ]
 
 
@@ -132,8 +135,26 @@ def lib():
         L.msk144_aggregator_destroy.restype = None
         L.msk144_aggregator_add.argtypes = [vp, C.POINTER(Line), sz]
         L.msk144_aggregator_poll.argtypes = [vp, C.c_int64, C.c_int, C.POINTER(Event), sz, C.POINTER(sz)]
+        L.msk144_pool_last_error.restype = C.c_char_p
+        L.msk144_pool_create.argtypes = [C.POINTER(Config), C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]
+        L.msk144_pool_destroy.argtypes = [vp]
+        L.msk144_pool_destroy.restype = None
+        L.msk144_pool_size.argtypes = [vp]
+        L.msk144_pool_member.argtypes = [vp, C.c_int32]
+        L.msk144_pool_member.restype = vp
+        L.msk144_pool_decode_host.argtypes = L.msk144_decode_host.argtypes
+        L.msk144_pool_push_interleaved.argtypes = [vp, vp, sz, C.c_int]
+        L.msk144_pool_poll.argtypes = [vp, C.POINTER(Line), sz, C.POINTER(sz)]
+        L.msk144_pool_reset_stream.argtypes = [vp]
+        L.msk144_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double)]
+        L.msk144_build_info.restype = C.c_char_p
         _lib = L
     return _lib
+
+
+def build_info() -> str:
+    """Toolkit the library was compiled with (the LDPC kernel's tanh reproduces that toolkit's libdevice)."""
+    return lib().msk144_build_info().decode("ascii")
 
 
 def _check(rc: int):
@@ -152,15 +173,9 @@ class Decoder:
 
     def __init__(self, center: Optional[float] = None, width: float = 200.0, step: float = 2.0, depth: int = 4,
                  thr: int = 1, read_mode: int = 1, method: int = 2, device: int = 0, max_batch_blocks: int = 128,
-                 compat_cache: bool = True, flags: int = 0):
+                 compat_cache: bool = False, flags: int = 0):
         L = lib()
-        cfg = Config()
-        L.msk144_config_defaults(C.byref(cfg))
-        cfg.center_frequency_hz = (1500.0 if read_mode == 1 else 0.0) if center is None else center
-        cfg.search_width_hz, cfg.search_step_hz, cfg.scan_depth = width, step, depth
-        cfg.nbadsync_threshold, cfg.read_mode, cfg.analytic_method = thr, read_mode, method
-        cfg.device, cfg.max_batch_blocks = device, max_batch_blocks
-        cfg.flags = (FLAG_COMPAT_DECODE_CACHE if compat_cache else 0) | flags
+        cfg = _make_config(center, width, step, depth, thr, read_mode, method, device, max_batch_blocks, compat_cache, flags)
         self.cfg = cfg
         self._h = C.c_void_p()
         _check(L.msk144_create(C.byref(cfg), C.byref(self._h)))
@@ -257,11 +272,15 @@ class Decoder:
                                           C.byref(n)))
         return blocks, powers
 
-    def scan(self, blocks: np.ndarray):
-        """blocks: complex64 [nblocks, 5184].  Returns (cands[nblocks, items], llr[n,128], llr_item[n])."""
+    def scan(self, blocks: np.ndarray, want_llr: bool = True):
+        """blocks: complex64 [nblocks, 5184].  Returns (cands[nblocks, items], llr[n,128], llr_item[n]);
+        want_llr=False returns only the candidates (no 512 B per gated candidate on the host)."""
         blocks = np.ascontiguousarray(blocks, np.complex64).reshape(-1, BLOCK_SAMPLES)
         nb = blocks.shape[0]
         cands = np.zeros((nb, self.items_per_block), CAND_DTYPE)
+        if not want_llr:
+            _check(lib().msk144_scan_host(self._h, blocks.ctypes.data, nb, cands.ctypes.data, None, None, 0, None))
+            return cands
         cap = nb * self.items_per_block
         llr = np.zeros((cap, 128), np.float32)
         item = np.zeros(cap, np.uint32)
@@ -290,6 +309,92 @@ class Decoder:
 
     def ldpc_decode_device(self, d_llr: int, ncw: int, d_out: int, stream: int = 0):
         _check(lib().msk144_ldpc_decode_device(self._h, d_llr, ncw, d_out, C.c_void_p(stream)))
+
+    def measure_fp32_peak(self) -> float:
+        """Sustained FP32 FMA rate of this decoder's GPU in TFLOP/s (dependency-free FFMA stream, CUDA events)."""
+        v = C.c_double(0.0)
+        _check(lib().msk144_measure_fp32_peak(self._h, C.byref(v)))
+        return float(v.value)
+
+
+def _make_config(center, width, step, depth, thr, read_mode, method, device, max_batch_blocks, compat_cache, flags) -> Config:
+    cfg = Config()
+    lib().msk144_config_defaults(C.byref(cfg))
+    cfg.center_frequency_hz = (1500.0 if read_mode == 1 else 0.0) if center is None else center
+    cfg.search_width_hz, cfg.search_step_hz, cfg.scan_depth = width, step, depth
+    cfg.nbadsync_threshold, cfg.read_mode, cfg.analytic_method = thr, read_mode, method
+    cfg.device, cfg.max_batch_blocks = device, max_batch_blocks
+    cfg.flags = (FLAG_COMPAT_DECODE_CACHE if compat_cache else 0) | flags
+    return cfg
+
+
+class Pool:
+    """One decoder per listed GPU behind one handle (msk144_pool_*): channels are split into contiguous ranges, one
+    host thread and one set of CUDA streams per GPU, lines merged on the host in single-decoder order."""
+
+    def __init__(self, devices: List[int], center: Optional[float] = None, width: float = 200.0, step: float = 2.0,
+                 depth: int = 4, thr: int = 1, read_mode: int = 1, method: int = 2, max_batch_blocks: int = 128,
+                 compat_cache: bool = False, flags: int = 0):
+        cfg = _make_config(center, width, step, depth, thr, read_mode, method, 0, max_batch_blocks, compat_cache, flags)
+        devs = (C.c_int32 * len(devices))(*devices)
+        self._h = C.c_void_p()
+        rc = lib().msk144_pool_create(C.byref(cfg), devs, len(devices), C.byref(self._h))
+        if rc != 0:
+            raise Msk144Error(f"msk144 pool error {rc}: {lib().msk144_pool_last_error().decode('utf-8', 'replace')}")
+        self.devices = list(devices)
+
+    def _check(self, rc):
+        if rc != 0:
+            raise Msk144Error(f"msk144 pool error {rc}: {lib().msk144_pool_last_error().decode('utf-8', 'replace')}")
+
+    def decode_host(self, samples: np.ndarray, nchan: int, line_cap: int = 4096, result_cap: int = 0):
+        samples = np.ascontiguousarray(samples)
+        spc = samples.nbytes // 2 // nchan
+        while True:
+            lines = (Line * line_cap)()
+            results = np.zeros(result_cap, RESULT_DTYPE)
+            nl, nr = C.c_size_t(0), C.c_size_t(0)
+            rc = lib().msk144_pool_decode_host(self._h, samples.ctypes.data, spc, nchan, lines, line_cap, C.byref(nl),
+                                               results.ctypes.data if result_cap else None, result_cap,
+                                               C.byref(nr) if result_cap else None)
+            if rc == -5 and (nl.value > line_cap or nr.value > result_cap):
+                line_cap, result_cap = max(line_cap, nl.value), (max(result_cap, nr.value) if result_cap else 0)
+                continue
+            self._check(rc)
+            return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
+
+    def push(self, data: bytes, nchan: int):
+        self._check(lib().msk144_pool_push_interleaved(self._h, data, len(data), nchan))
+
+    def poll(self, cap: int = 1024) -> List[dict]:
+        out = []
+        while True:
+            lines = (Line * cap)()
+            n = C.c_size_t(0)
+            self._check(lib().msk144_pool_poll(self._h, lines, cap, C.byref(n)))
+            out += [_line_dict(lines[i]) for i in range(n.value)]
+            if n.value < cap:
+                return out
+
+    def reset_stream(self):
+        self._check(lib().msk144_pool_reset_stream(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().msk144_pool_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
 
 
 # ---- mirror of the reference's operator interface ---------------------------------------------------

@@ -33,6 +33,7 @@ static void show_help(const char* prog) {
     std::cout << "                   --nbadsync-threshold=[1..4] How many errors in sync pattern are acceptable to be passed to LDPC decoder." << std::endl;
     std::cout << " Extensions of this build:" << std::endl;
     std::cout << "                   --device=0                  CUDA device ordinal." << std::endl;
+    std::cout << "                   --devices=0,1,...           With --channels=N: split the channels over these GPUs (one host thread and stream set each)." << std::endl;
     std::cout << "                   --batch-blocks=128          Blocks per GPU launch group when input arrives faster than real time." << std::endl;
     std::cout << "                   --per-payload-text          Decode every payload's own text (the reference reuses the first decode of a block)." << std::endl;
     std::cout << "                   --channels=1                stdin carries N channels, one sample of each per time step; lines end with channel=<c>." << std::endl;
@@ -56,6 +57,7 @@ int main(int argc, char* const argv[]) {
     bool center_set = false, json = false;
     int dedupe_gap = -1;  // < 0: print every per-block line, as the reference does
     int nchan = 1;
+    std::vector<int32_t> devices;  // --devices: more than one entry selects the multi-GPU pool
     static struct option long_options[] = {{"help", no_argument, 0, 0},                     // 0
                                            {"center-frequency", required_argument, 0, 0},   // 1
                                            {"search-step", required_argument, 0, 0},        // 2
@@ -72,6 +74,7 @@ int main(int argc, char* const argv[]) {
                                            {"dedupe", optional_argument, 0, 0},             // 13
                                            {"unpack77-lib", required_argument, 0, 0},       // 14
                                            {"channels", required_argument, 0, 0},           // 15
+                                           {"devices", required_argument, 0, 0},            // 16
                                            {0, 0, 0, 0}};
     while (true) {
         int option_index = 0;
@@ -100,6 +103,13 @@ int main(int argc, char* const argv[]) {
                 }
                 break;
             case 15: nchan = atoi(optarg) > 0 ? atoi(optarg) : 1; break;
+            case 16:
+                devices.clear();
+                for (const char* q = optarg; *q;) {
+                    devices.push_back(static_cast<int32_t>(strtol(q, const_cast<char**>(&q), 10)));
+                    while (*q == ',' || *q == ' ') q++;
+                }
+                break;
             default: show_help(argv[0]); return 0;
         }
     }
@@ -112,7 +122,15 @@ int main(int argc, char* const argv[]) {
         }
     }
     msk144_decoder* dec = nullptr;
-    if (msk144_create(&cfg, &dec) != MSK144_OK) {
+    msk144_pool* pool = nullptr;
+    if (devices.size() == 1) cfg.device = devices[0];
+    if (devices.size() > 1) {
+        if (msk144_pool_create(&cfg, devices.data(), static_cast<int32_t>(devices.size()), &pool) != MSK144_OK) {
+            std::cerr << msk144_pool_last_error() << std::endl;
+            return 2;
+        }
+        dec = msk144_pool_member(pool, 0);
+    } else if (msk144_create(&cfg, &dec) != MSK144_OK) {
         std::cerr << msk144_last_error() << std::endl;
         return 2;
     }
@@ -131,8 +149,9 @@ int main(int argc, char* const argv[]) {
     std::cerr << "Badsync Threshold: " << cfg.nbadsync_threshold << std::endl
               << "Frequency hypotheses: " << info.num_freqs << std::endl
               << "Candidates per block: " << info.items_per_block << std::endl
-              << "GPU SMs: " << info.sm_count << std::endl
-              << std::endl;
+              << "GPU SMs: " << info.sm_count << std::endl;
+    if (pool) std::cerr << "GPUs: " << msk144_pool_size(pool) << " (" << nchan << " channels split in contiguous ranges)" << std::endl;
+    std::cerr << std::endl;
 
     const size_t hop_bytes = MSK144_HOP_SAMPLES * 2 * static_cast<size_t>(nchan);  // both modes: 2 bytes per sample
     const size_t block_bytes = MSK144_BLOCK_SAMPLES * 2 * static_cast<size_t>(nchan);
@@ -140,6 +159,7 @@ int main(int argc, char* const argv[]) {
     const size_t group_blocks = static_cast<size_t>(cfg.max_batch_blocks > 0 ? cfg.max_batch_blocks : 128);
     std::vector<unsigned char> buf(hop_bytes * std::max<size_t>(1, group_blocks / static_cast<size_t>(nchan)));
     std::vector<msk144_line> lines(4096);
+    std::vector<unsigned char> carry;
     size_t total_bytes = 0;
     int rc_exit = 0;
     msk144_aggregator* agg = nullptr;
@@ -174,16 +194,26 @@ int main(int argc, char* const argv[]) {
         const auto t0 = std::chrono::steady_clock::now();
         const int64_t before = 0;
         (void)before;
-        const int prc = nchan > 1 ? msk144_push_interleaved(dec, buf.data(), static_cast<size_t>(n), nchan)
-                                  : msk144_push(dec, buf.data(), static_cast<size_t>(n));
+        int prc;
+        if (pool) {
+            // the pool takes whole time steps (one sample of every channel): keep a partial one for the next read
+            carry.insert(carry.end(), buf.data(), buf.data() + n);
+            const size_t frame = 2 * static_cast<size_t>(nchan), whole = carry.size() / frame * frame;
+            prc = whole ? msk144_pool_push_interleaved(pool, carry.data(), whole, nchan) : MSK144_OK;
+            carry.erase(carry.begin(), carry.begin() + whole);
+        } else {
+            prc = nchan > 1 ? msk144_push_interleaved(dec, buf.data(), static_cast<size_t>(n), nchan)
+                            : msk144_push(dec, buf.data(), static_cast<size_t>(n));
+        }
         if (prc != MSK144_OK) {
-            std::cerr << msk144_last_error() << std::endl;
+            std::cerr << (pool ? msk144_pool_last_error() : msk144_last_error()) << std::endl;
             rc_exit = 2;
             break;
         }
         size_t got = 0;
         do {
-            msk144_poll(dec, lines.data(), lines.size(), &got);
+            if (pool) msk144_pool_poll(pool, lines.data(), lines.size(), &got);
+            else msk144_poll(dec, lines.data(), lines.size(), &got);
             if (agg) msk144_aggregator_add(agg, lines.data(), got);
             else for (size_t i = 0; i < got; i++) print_line(lines[i]);
         } while (got == lines.size());
@@ -210,6 +240,7 @@ int main(int argc, char* const argv[]) {
     }
     std::cerr << "Incomplete read error. rc=" << rc_items << std::endl;
     std::cout << "Done" << std::endl;
-    msk144_destroy(dec);
+    if (pool) msk144_pool_destroy(pool);
+    else msk144_destroy(dec);
     return rc_exit;
 }

@@ -13,6 +13,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <deque>
+#include <memory>
 #include <string>
 #include <vector>
 
@@ -109,6 +110,21 @@ struct RawResult {
     ResultRec r;
 };
 
+// What one channel carries from block to block: the SNR recurrence (snr_tracker.cu:39-50) and the call-sign hash
+// tables of its text decoder (module state of packjt77 in the reference process).
+struct ChanState {
+    mskhost::SnrTracker snr;
+    void* hash = nullptr;
+    ChanState() : hash(msk144_hash_state_new()) {}
+    ChanState(const ChanState&) = delete;
+    ChanState& operator=(const ChanState&) = delete;
+    ~ChanState() { msk144_hash_state_free(hash); }
+    void reset() {
+        snr.reset();
+        msk144_hash_state_clear(hash);
+    }
+};
+
 }  // namespace
 
 struct msk144_decoder {
@@ -161,11 +177,11 @@ struct msk144_decoder {
     // multi-channel streaming state (msk144_push_interleaved): raw interleaved bytes, one SNR recurrence per channel
     int il_nchan = 0;
     std::vector<uint8_t> il_pending;
-    std::vector<mskhost::SnrTracker> il_snr;
+    std::vector<std::unique_ptr<ChanState>> il_state;
     int64_t il_next_block = 0;
     bool wav_checked = false;      // MSK144_FLAG_SKIP_WAV_HEADER: the start of the stream has been examined
     int64_t next_block = 0;
-    mskhost::SnrTracker stream_snr;
+    ChanState stream_state;
     std::deque<msk144_line> out_lines;
 
     ~msk144_decoder() { release(); }
@@ -195,7 +211,7 @@ struct msk144_decoder {
         }
     }
     int decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
-                      mskhost::SnrTracker* carry, std::vector<msk144_line>* lines, std::vector<msk144_result>* results);
+                      ChanState* const* carry, std::vector<msk144_line>* lines, std::vector<msk144_result>* results);
 };
 
 void msk144_decoder::release() {
@@ -388,7 +404,7 @@ int msk144_decoder::fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, i
 }
 
 int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaStream_t st, int64_t block_index_base,
-                                  mskhost::SnrTracker* carry, std::vector<msk144_line>* lines,
+                                  ChanState* const* carry, std::vector<msk144_line>* lines,
                                   std::vector<msk144_result>* results) {
     times = msk144_stage_times{};
     ev_used = 0;
@@ -401,7 +417,7 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
     std::vector<RawResult> raw;
     std::vector<float> powers;
     const bool compat = (cfg.flags & MSK144_FLAG_COMPAT_DECODE_CACHE) != 0;
-    mskhost::SnrTracker local;
+    ChanState local;
     // host post-processing of one fetched group, block by block in stream order (main.cu:388-419); it runs
     // while the GPU works on the next group
     auto process = [&](int64_t g0, int nb) {
@@ -413,8 +429,9 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
         for (int64_t gb = g0; gb < g0 + nb; gb++) {
             const int ch = static_cast<int>(gb / bpc);
             const int64_t k = gb % bpc;
-            if (k == 0) local = mskhost::SnrTracker();  // every channel starts a fresh SNR recurrence ...
-            mskhost::SnrTracker* snr = carry ? &carry[ch] : &local;  // ... unless the caller carries one per channel
+            if (k == 0) local.reset();  // every channel starts a fresh SNR recurrence and fresh call-sign tables ...
+            ChanState* cs = carry ? carry[ch] : &local;  // ... unless the caller carries them per channel
+            mskhost::SnrTracker* snr = &cs->snr;
             snr->process_powers(&powers[static_cast<size_t>(gb - g0) * 8]);
             std::vector<mskhost::Present> present;
             while (ri < raw.size() && raw[ri].gblock == gb) {
@@ -451,7 +468,7 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
                 ri++;
             }
             if (lines && !present.empty()) {
-                const auto bl = mskhost::block_lines(present, compat, snr->snr_i());
+                const auto bl = mskhost::block_lines(present, compat, snr->snr_i(), cs->hash);
                 for (const auto& l : bl) {
                     msk144_line o;
                     std::memset(&o, 0, sizeof(o));
@@ -736,10 +753,10 @@ int msk144_run_device(msk144_decoder* dec, const void* d_samples, size_t spc, in
 int msk144_reset_stream(msk144_decoder* dec) {
     if (!dec) return fail(MSK144_EINVAL, "null argument");
     dec->pending.clear();
-    dec->il_pending.clear(), dec->il_snr.clear(), dec->il_nchan = 0, dec->il_next_block = 0;
+    dec->il_pending.clear(), dec->il_state.clear(), dec->il_nchan = 0, dec->il_next_block = 0;
     dec->wav_checked = false;
     dec->next_block = 0;
-    dec->stream_snr.reset();
+    dec->stream_state.reset();
     dec->out_lines.clear();
     return MSK144_OK;
 }
@@ -765,8 +782,8 @@ int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
     CK(cudaMemcpyAsync(dec->d_raw, dec->pending.data(), used_samples * 2, cudaMemcpyHostToDevice, dec->stream));
     dec->h2d_bytes += used_samples * 2;
     std::vector<msk144_line> lv;
-    if (int rc = dec->decode_common(dec->d_raw, used_samples, 1, dec->stream, dec->next_block, &dec->stream_snr, &lv,
-                                    nullptr))
+    ChanState* const carry1[1] = {&dec->stream_state};
+    if (int rc = dec->decode_common(dec->d_raw, used_samples, 1, dec->stream, dec->next_block, carry1, &lv, nullptr))
         return rc;
     for (const auto& l : lv) dec->out_lines.push_back(l);
     dec->next_block += static_cast<int64_t>(nblocks);
@@ -779,7 +796,8 @@ int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbyte
     if (!dec || (!bytes && nbytes) || nchan < 1) return fail(MSK144_EINVAL, "bad argument");
     if (dec->il_nchan == 0) {
         dec->il_nchan = nchan;
-        dec->il_snr.assign(static_cast<size_t>(nchan), mskhost::SnrTracker());
+        dec->il_state.clear();
+        for (int c = 0; c < nchan; c++) dec->il_state.emplace_back(new ChanState());
     } else if (dec->il_nchan != nchan) {
         return fail(MSK144_EINVAL, "channel count changed in mid-stream (msk144_reset_stream first)");
     }
@@ -799,7 +817,9 @@ int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbyte
     dec->h2d_bytes += ubytes;
     if (int rc = msk144_deinterleave_device(dec, d_il, d_cm, used, nchan, dec->stream)) return rc;
     std::vector<msk144_line> lv;
-    if (int rc = dec->decode_common(d_cm, used, nchan, dec->stream, dec->il_next_block, dec->il_snr.data(), &lv, nullptr))
+    std::vector<ChanState*> carry(static_cast<size_t>(nchan));
+    for (int c = 0; c < nchan; c++) carry[c] = dec->il_state[c].get();
+    if (int rc = dec->decode_common(d_cm, used, nchan, dec->stream, dec->il_next_block, carry.data(), &lv, nullptr))
         return rc;
     for (const auto& l : lv) dec->out_lines.push_back(l);
     dec->il_next_block += static_cast<int64_t>(nblocks);
@@ -1026,6 +1046,41 @@ int msk144_selftest_ldpc_math(msk144_decoder* dec, uint64_t* tanh_mismatches, ui
     if (tanh_mismatches) *tanh_mismatches = h[0];
     if (platanh_mismatches) *platanh_mismatches = h[1];
     return MSK144_OK;
+}
+
+int msk144_measure_fp32_peak(msk144_decoder* dec, double* tflops) {
+    if (!dec || !tflops) return fail(MSK144_EINVAL, "null argument");
+    CK(cudaSetDevice(dec->cfg.device));
+    float* d_sink = nullptr;
+    CK(cudaMalloc(&d_sink, sizeof(float)));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0));
+    CK(cudaEventCreate(&e1));
+    const int grid = dec->sm_count * 4, threads = 512, iters = 8192;  // 2048 threads = 16 warps per scheduler
+    double best = 0.0;
+    for (int rep = 0; rep < 4; rep++) {  // first pass warms up; best of the rest
+        cudaEventRecord(e0, dec->stream);
+        fp32_peak_kernel<<<grid, threads, 0, dec->stream>>>(d_sink, iters, 0.999f, 0.001f);
+        cudaEventRecord(e1, dec->stream);
+        if (cudaStreamSynchronize(dec->stream) != cudaSuccess) break;
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double fl = 2.0 * 32.0 * iters * static_cast<double>(grid) * threads;
+        if (rep > 0 && ms > 0.f) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0), cudaEventDestroy(e1);
+    cudaFree(d_sink);
+    dec->launches += 4;
+    if (cudaGetLastError() != cudaSuccess || best <= 0.0) return fail(MSK144_ECUDA, "fp32 peak probe failed");
+    *tflops = best;
+    return MSK144_OK;
+}
+
+const char* msk144_build_info(void) {
+#define MSK_STR2(x) #x
+#define MSK_STR(x) MSK_STR2(x)
+    return "nvcc " MSK_STR(__CUDACC_VER_MAJOR__) "." MSK_STR(__CUDACC_VER_MINOR__) "." MSK_STR(__CUDACC_VER_BUILD__)
+           "; sm_100a; " __DATE__;
 }
 
 #ifdef MSK_SCAN_PROF

@@ -35,7 +35,7 @@ void SnrTracker::process_powers(const float* arr) {
     if (snr_ < -8.0f) snr_ = -8.0f;
 }
 
-bool decode_message(const uint8_t* m, std::string* text) {
+bool decode_message(const uint8_t* m, std::string* text, void* hash_state) {
     const int n3 = (m[71] << 2) | (m[72] << 1) | m[73];
     const int i3 = (m[74] << 2) | (m[75] << 1) | m[76];
     if ((i3 == 0 && (n3 == 1 || n3 == 3 || n3 == 4 || n3 > 5)) || i3 == 3 || i3 > 5) return false;
@@ -44,7 +44,7 @@ bool decode_message(const uint8_t* m, std::string* text) {
     const int nrx = 1;  // receive semantics
     char msg[37];
     int ok = 0;
-    msk144_unpack77(c77, &nrx, msg, &ok);
+    msk144_unpack77_in(hash_state, c77, &nrx, msg, &ok);
     if (!ok) return false;
     int len = 37;
     while (len > 0 && msg[len - 1] == ' ') len--;
@@ -52,7 +52,7 @@ bool decode_message(const uint8_t* m, std::string* text) {
     return true;
 }
 
-std::vector<Line> block_lines(const std::vector<Present>& items, bool compat, int snr) {
+std::vector<Line> block_lines(const std::vector<Present>& items, bool compat, int snr, void* hash_state) {
     std::vector<Line> scope;
     std::map<std::string, std::pair<bool, std::string>> cache;
     bool have_first = false;
@@ -63,7 +63,7 @@ std::vector<Line> block_lines(const std::vector<Present>& items, bool compat, in
             // The reference keys its per-block cache with a comparator that never compares
             // (main.cu:437-445), so the first candidate's outcome is reused for the whole block.
             if (!have_first) {
-                first.first = decode_message(it.message, &first.second);
+                first.first = decode_message(it.message, &first.second, hash_state);
                 have_first = true;
             }
             res = first;
@@ -72,7 +72,7 @@ std::vector<Line> block_lines(const std::vector<Present>& items, bool compat, in
             auto f = cache.find(key);
             if (f == cache.end()) {
                 std::pair<bool, std::string> r;
-                r.first = decode_message(it.message, &r.second);
+                r.first = decode_message(it.message, &r.second, hash_state);
                 f = cache.emplace(key, r).first;
             }
             res = f->second;

@@ -20,8 +20,8 @@ private:
     float noise_ = 0.0f, snr_ = 0.0f;
 };
 
-// decode_softbits.cpp:23-55
-bool decode_message(const uint8_t* msg77, std::string* text);
+// decode_softbits.cpp:23-55.  hash_state: the stream's call-sign tables (unpack77.h), NULL = process-wide.
+bool decode_message(const uint8_t* msg77, std::string* text, void* hash_state = nullptr);
 
 struct Present {  // one LDPC success of a block, in item-index order
     uint32_t item;
@@ -40,7 +40,8 @@ struct Line {  // result_filter.h:17-29
 
 // main.cu:480-525 (host loop incl. decode_cache) followed by ResultFilter::blockEnd
 // (result_filter.cpp:43-74).  `items` must be sorted by item index.
-std::vector<Line> block_lines(const std::vector<Present>& items, bool compat_decode_cache, int snr);
+std::vector<Line> block_lines(const std::vector<Present>& items, bool compat_decode_cache, int snr,
+                              void* hash_state = nullptr);
 
 // main.cu:406-419.  date14: "%Y%m%d%H%M%S".
 std::string format_line(int snr, float f0, int num_avg, int nbadsync, int pattern_idx, const char* date14,

@@ -20,6 +20,7 @@
 #include <cstring>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 
 namespace {
 
@@ -28,9 +29,12 @@ constexpr int MAX22 = 4194304;
 constexpr int MAXGRID4 = 32400;
 constexpr int MAXHASH = 20;
 
+// Call-sign hash tables (WSJT-X keeps them in module variables: one set per process).  Here one set per stream:
+// every decoder channel owns a HashState (msk144_hash_state_new) and names it for the duration of a text decode, so
+// what channel A heard never changes how channel B's <...> fields print, and concurrent decoders do not share state.
+// The process-wide set remains for callers of the bare gfortran-ABI symbol.
 struct HashState {
-    std::string calls10[1024];
-    std::string calls12[4096];
+    std::unordered_map<int, std::string> calls10, calls12;   // sparse: a channel hears a handful of calls
     int ihash22[MAXHASH];
     std::string calls22[MAXHASH];
     HashState() {
@@ -38,9 +42,11 @@ struct HashState {
     }
 };
 HashState* g_hash = nullptr;
+thread_local HashState* t_hash = nullptr;  // the state named by the caller for this thread, if any
 std::mutex g_mu;
 
 HashState& hs() {
+    if (t_hash) return *t_hash;
     if (!g_hash) g_hash = new HashState();
     return *g_hash;
 }
@@ -112,9 +118,10 @@ void save_hash_call(const std::string& c13) {
 
 std::string hash12(int n12) {
     if (n12 < 0 || n12 > 4095) return "<...>";
-    const std::string& c = hs().calls12[n12];
-    if (c.empty()) return "<...>";
-    return "<" + c + ">";
+    const auto& tab = hs().calls12;
+    const auto f = tab.find(n12);
+    if (f == tab.end() || f->second.empty()) return "<...>";
+    return "<" + f->second + ">";
 }
 std::string hash22(int n22) {
     HashState& h = hs();
@@ -435,6 +442,18 @@ void msk144_unpack77_reset(void) {
     std::lock_guard<std::mutex> lk(g_mu);
     delete g_hash;
     g_hash = nullptr;
+}
+
+void* msk144_hash_state_new(void) { return new HashState(); }
+void msk144_hash_state_free(void* st) { delete static_cast<HashState*>(st); }
+void msk144_hash_state_clear(void* st) {
+    if (st) *static_cast<HashState*>(st) = HashState();
+}
+void msk144_unpack77_in(void* st, const char c77[77], const int* nrx, char msg[37], int* ok) {
+    HashState* prev = t_hash;
+    t_hash = static_cast<HashState*>(st);
+    msk144_unpack77(c77, nrx, msg, ok);
+    t_hash = prev;
 }
 
 // gfortran module-procedure ABI: character arguments carry hidden trailing lengths (f_interop.cpp:10-29)

@@ -9,6 +9,12 @@ extern "C" {
 void msk144_unpack77(const char c77[77], const int* nrx, char msg[37], int* ok);
 // Forget all hashed call signs (the tables otherwise persist for the life of the process).
 void msk144_unpack77_reset(void);
+// Per-stream call-sign hash tables: msk144_unpack77_in() is msk144_unpack77() against the tables of `state`
+// (NULL = the process-wide set).  The built-in decoder only; an external library keeps its own module state.
+void* msk144_hash_state_new(void);
+void msk144_hash_state_free(void* state);
+void msk144_hash_state_clear(void* state);
+void msk144_unpack77_in(void* state, const char c77[77], const int* nrx, char msg[37], int* ok);
 // Route text decoding through a user-supplied library exporting __packjt77_MOD_unpack77 (NULL / "" = built-in).
 // Returns 0, or -1 if the library or the symbol cannot be loaded (the built-in stays active).
 int msk144_set_unpack77_library(const char* path);

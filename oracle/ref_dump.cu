@@ -2,10 +2,17 @@
 // /root/reference/src where they lie; nothing is copied into this repository) and dumps their
 // stage outputs so that tests/golden/ can pin the oracle and the product bit-for-bit:
 //
-//   ref_dump stream <read_mode> <method> <center> <width> <step> <depth> <thr> <in.raw> <out_prefix> [max_blocks]
+//   ref_dump stream <read_mode> <method> <center> <width> <step> <depth> <thr> <in.raw> <out_prefix> [max_blocks] [compact]
 //       per block: filtered block (complex64 x 5184)        -> <out_prefix>.blocks.c64
 //                  every ResultItem after the LDPC kernel    -> <out_prefix>.items.bin  (632 B each)
 //                  SNRTracker::getSNRI()                     -> <out_prefix>.snr.i32
+//       with a 12th argument "compact" (long streams: 15 MB of items per deep block would not fit a fixture):
+//                  only the items with is_message_present, 120 B each {block, item, pos, f0, nbadsync, xb,
+//                  num_avg, iters, nhard, pad, message[80]}  -> <out_prefix>.present.bin
+//                  number of items with nbadsync <= thr       -> <out_prefix>.ngated.i32
+//                  the block's output lines from the reference's own do_decode + ResultFilter (main.cu:390-419),
+//                  "<block>\t<line, date masked>"            -> <out_prefix>.lines.txt
+//                  SNR as above; no filtered blocks
 //   ref_dump ldpc <in_llr.f32> <out.bin>
 //       feeds [ncw][128] LLRs straight into ldpc_kernel; per codeword 80+4+4+4 bytes
 //       {message[80], found, iters, nhard}
@@ -20,6 +27,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <iomanip>
+#include <sstream>
 #include <vector>
 
 static std::vector<char> read_file(const char* path) {
@@ -93,6 +102,7 @@ static int run_stream(int argc, char** argv) {
     const std::vector<char> raw = read_file(argv[9]);
     const std::string prefix = argv[10];
     const long max_blocks = argc > 11 ? atol(argv[11]) : 0;
+    const bool compact = argc > 12 && !strcmp(argv[12], "compact");
     const size_t nsamp = raw.size() / 2;
     long nblocks = nsamp >= Num6x864 ? (long)((nsamp - Num6x864) / (Num6x864 / 2)) + 1 : 0;
     if (max_blocks > 0 && nblocks > max_blocks) nblocks = max_blocks;
@@ -102,9 +112,12 @@ static int run_stream(int argc, char** argv) {
     thrust::host_vector<Complex> a_in_host(Num6x864), a_out_host(Num6x864), host_complex_8192(8192);
     thrust::device_vector<Complex> a_in_device(Num6x864), a_out_device(Num6x864);
     SNRTracker snr_tracker;
-    FILE* fb = fopen((prefix + ".blocks.c64").c_str(), "wb");
-    FILE* fi = fopen((prefix + ".items.bin").c_str(), "wb");
+    FILE* fb = compact ? nullptr : fopen((prefix + ".blocks.c64").c_str(), "wb");
+    FILE* fi = fopen((prefix + (compact ? ".present.bin" : ".items.bin")).c_str(), "wb");
     FILE* fs = fopen((prefix + ".snr.i32").c_str(), "wb");
+    FILE* fg = compact ? fopen((prefix + ".ngated.i32").c_str(), "wb") : nullptr;
+    FILE* fl = compact ? fopen((prefix + ".lines.txt").c_str(), "w") : nullptr;
+    ResultFilter result_filter;
     static_assert(sizeof(ResultKeeper::ResultItem) == 632, "ResultItem layout");
     for (long b = 0; b < nblocks; b++) {
         const Complex* host_data = nullptr;
@@ -143,24 +156,73 @@ static int run_stream(int argc, char** argv) {
             dev_data = thrust::raw_pointer_cast(a_out_device.data());
         }
         snr_tracker.process_data(host_data, Num6x864);
-        // do_decode's GPU part, main.cu:461-471
-        ctx.resultKeeper().clear_result();
-        scan_kernel<<<ctx.getBlocks(), ctx.getThreads()>>>(ctx, dev_data);
-        softbits_kernel<<<ctx.getSoftBitsBlocks(), ctx.getSoftBitsThreads()>>>(ctx, dev_data);
-        index_kernel<<<1, NumIndexThreads>>>(ctx);
-        const auto ldpcBlocks = ctx.resultKeeper().getIndexedCandidatesBlocks();
-        if (ldpcBlocks.x > 0) ldpc_kernel<<<ldpcBlocks, 128>>>(ctx);
-        if (cudaDeviceSynchronize() != cudaSuccess) {
-            fprintf(stderr, "cuda error at block %ld: %s\n", b, cudaGetErrorString(cudaGetLastError()));
-            return 3;
+        if (compact) {
+            // the reference's own per-block host loop (main.cu:390-419): do_decode + ResultFilter, lines tagged with
+            // the block they were printed for
+            result_filter.blockBegin();
+            do_decode(ctx, dev_data, result_filter, snr_tracker);
+            result_filter.blockEnd();
+            for (auto const& elm : result_filter.getBlockResult()) {
+                std::ostringstream os;
+                os << "***  "
+                   << "snr=" << std::setw(2) << elm.snr << "; "
+                   << "f0=" << std::setw(6) << elm.f0 << "; "
+                   << "num_avg=" << elm.num_avg << "; "
+                   << "nbadsync=" << elm.nbadsync << "; "
+                   << "pattern_idx=" << elm.pattern_idx << "; "
+                   << "date=xxxxxxxxxxxxxx; "
+                   << "msg='" << elm.message << "'"
+                   << "; ";
+                fprintf(fl, "%ld\t%s\n", b, os.str().c_str());
+            }
+        } else {
+            // do_decode's GPU part, main.cu:461-471
+            ctx.resultKeeper().clear_result();
+            scan_kernel<<<ctx.getBlocks(), ctx.getThreads()>>>(ctx, dev_data);
+            softbits_kernel<<<ctx.getSoftBitsBlocks(), ctx.getSoftBitsThreads()>>>(ctx, dev_data);
+            index_kernel<<<1, NumIndexThreads>>>(ctx);
+            const auto ldpcBlocks = ctx.resultKeeper().getIndexedCandidatesBlocks();
+            if (ldpcBlocks.x > 0) ldpc_kernel<<<ldpcBlocks, 128>>>(ctx);
+            if (cudaDeviceSynchronize() != cudaSuccess) {
+                fprintf(stderr, "cuda error at block %ld: %s\n", b, cudaGetErrorString(cudaGetLastError()));
+                return 3;
+            }
         }
         thrust::host_vector<ResultKeeper::ResultItem> all = ctx.resultKeeper().get_all_results();
-        fwrite(host_data, sizeof(Complex), Num6x864, fb);
-        fwrite(all.data(), sizeof(ResultKeeper::ResultItem), all.size(), fi);
+        if (compact) {
+            int ngated = 0;
+            for (size_t i = 0; i < all.size(); i++) {
+                const auto& it = all[i];
+                if (it.nbadsync <= thr) ngated++;
+                if (!it.is_message_present) continue;
+                struct {
+                    int32_t block, item;
+                    uint32_t pos;
+                    float f0;
+                    int32_t nbadsync;
+                    float xb;
+                    int32_t num_avg, iters, nhard, pad;
+                    char message[80];
+                } rec;
+                static_assert(sizeof(rec) == 120, "compact record layout");
+                memset(&rec, 0, sizeof(rec));
+                rec.block = (int32_t)b, rec.item = (int32_t)i, rec.pos = it.pos, rec.f0 = it.f0, rec.nbadsync = it.nbadsync;
+                rec.xb = it.xb, rec.num_avg = it.num_avg, rec.iters = it.ldpc_num_iterations, rec.nhard = it.ldpc_num_hard_errors;
+                memcpy(rec.message, it.message, 77);
+                fwrite(&rec, sizeof(rec), 1, fi);
+            }
+            fwrite(&ngated, 4, 1, fg);
+        } else {
+            fwrite(host_data, sizeof(Complex), Num6x864, fb);
+            fwrite(all.data(), sizeof(ResultKeeper::ResultItem), all.size(), fi);
+        }
         const int snri = snr_tracker.getSNRI();
         fwrite(&snri, 4, 1, fs);
     }
-    fclose(fb), fclose(fi), fclose(fs);
+    if (fb) fclose(fb);
+    if (fg) fclose(fg);
+    if (fl) fclose(fl);
+    fclose(fi), fclose(fs);
     fprintf(stderr, "ref_dump: %ld blocks, %zu items per block\n", nblocks, (size_t)ctx.getBlocks().x * ctx.scanDepth() * NumCandidatesPerPattern);
     return 0;
 }

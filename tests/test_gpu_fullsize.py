@@ -35,7 +35,7 @@ def _key_nosnr(lines, shift=0):
 
 def _stream_properties(gpu, orc, x, pings, per_sample, dec_kw, orc_kw):
     hop, nblk = 2592 * per_sample, 5184 * per_sample
-    with gpu.Decoder(max_batch_blocks=128, **dec_kw) as d:
+    with gpu.Decoder(compat_cache=True, max_batch_blocks=128, **dec_kw) as d:
         full, _ = d.decode_host(x, line_cap=1 << 15, result_cap=0)
         again, _ = d.decode_host(x, line_cap=1 << 15, result_cap=0)
         nb = (len(x) - nblk) // hop + 1
@@ -105,7 +105,7 @@ def test_cfg4_ten_million_codewords_properties(gpu, orc, synth):
     per_point = 1_250_000
     g = torch.Generator(device=dev).manual_seed(146)
     fer, total = [], 0
-    with gpu.Decoder(width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, width=20, depth=1) as d:
         for ebn0 in range(8):
             msgs = torch.randint(0, 2, (per_point, 77), device=dev, generator=g, dtype=torch.uint8)
             cws = _torch_encode(torch, synth, msgs)
@@ -154,7 +154,7 @@ def test_cfg5_1024_channels_one_call(gpu, synth):
     seconds, distinct, copies = 12.0, 128, 8
     chans = [synth.cfg5_channel(c, seconds=seconds)[0] for c in range(distinct)]
     x = np.concatenate(chans * copies)                                    # channel c + 128 k is a copy of channel c
-    with gpu.Decoder(center=1500.0, max_batch_blocks=128, **DEEP) as d:
+    with gpu.Decoder(compat_cache=True, center=1500.0, max_batch_blocks=128, **DEEP) as d:
         multi, _ = d.decode_host(x, nchan=distinct * copies, line_cap=1 << 16, result_cap=0)
         single = {c: d.decode_host(chans[c], line_cap=4096, result_cap=0)[0] for c in (0, 1, 63, 127)}
     by_chan = {}

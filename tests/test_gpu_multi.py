@@ -1,0 +1,130 @@
+"""GPU: more than one decoder at work -- the in-process pool (msk144_pool_*, one host thread per member) and the
+multi-process sharding (torch.distributed, one rank per GPU) must both return exactly what ONE decoder returns.
+On a one-GPU box the members / ranks share GPU 0; with two or more GPUs they are spread (nccl for the ranks)."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+KW = dict(width=100, step=2, depth=3, thr=2)
+NCHAN, SECONDS = 5, 3.0
+
+
+@pytest.fixture(scope="module")
+def gpu(product):
+    import torch
+    assert torch.cuda.is_available()
+    return product
+
+
+def channels(synth, n=NCHAN):
+    return np.stack([synth.cfg5_channel(c, seconds=SECONDS)[0] for c in range(n)])
+
+
+def strip(lines):
+    return [(l["channel"], l["block"], l["text"], l["snr"], l["f0"], l["num_avg"], l["nbadsync"], l["pattern_idx"], l["payload"])
+            for l in lines]
+
+
+@pytest.mark.gpu
+def test_pool_batch_equals_single_decoder(gpu, synth):
+    import torch
+    x = channels(synth)
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        single, sres = d.decode_host(x, nchan=NCHAN)
+    assert len(single) > 0 and len({l["channel"] for l in single}) > 1
+    ndev = torch.cuda.device_count()
+    for devices in ([0], [0, 0, 0], [i % ndev for i in range(2)], [0] * 7):   # 7 members > 5 channels: two stay idle
+        with gpu.Pool(devices, compat_cache=True, **KW) as p:
+            pooled, pres = p.decode_host(x, nchan=NCHAN, result_cap=1 << 16)
+        assert strip(pooled) == strip(single), devices
+        assert pres.tobytes() == sres.tobytes(), devices
+
+
+@pytest.mark.gpu
+def test_pool_streaming_equals_single_decoder(gpu, synth):
+    x = channels(synth)
+    il = np.ascontiguousarray(x.T)          # [t][c]: one sample of every channel per time step
+    raw = il.tobytes()
+    frame = 2 * NCHAN
+    hop = 2592 * frame
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        single = []
+        for off in range(0, len(raw), hop):
+            d.push(raw[off:off + hop], nchan=NCHAN)
+            single += d.poll()
+    with gpu.Pool([0, 0], compat_cache=True, **KW) as p:
+        pooled = []
+        for off in range(0, len(raw), hop):
+            p.push(raw[off:off + hop], NCHAN)
+            pooled += p.poll()
+        with pytest.raises(gpu.Msk144Error):
+            p.push(raw[:frame + 1], NCHAN)      # not a whole number of time steps
+        p.reset_stream()
+        p.push(raw[:2 * hop], NCHAN)            # usable again after a reset
+    assert len(single) > 0 and strip(pooled) == strip(single)
+
+
+@pytest.mark.gpu
+def test_cli_devices_equals_single_device(gpu, synth):
+    import subprocess
+    x = channels(synth)
+    raw = np.ascontiguousarray(x.T).tobytes()
+    base = [gpu.CLI_PATH, "--search-width=100", "--search-step=2", "--scan-depth=3", "--nbadsync-threshold=2", f"--channels={NCHAN}"]
+    one = subprocess.run(base, input=raw, capture_output=True)
+    two = subprocess.run(base + ["--devices=0,0"], input=raw, capture_output=True)
+    assert one.returncode == 0 and two.returncode == 0, two.stderr.decode()[-300:]
+    mask = lambda b: [l.split("date=")[0] + l.split("date=")[1][14:] if "date=" in l else l for l in b.decode().splitlines()]
+    assert len(mask(one.stdout)) > 1 and mask(one.stdout) == mask(two.stdout)
+    assert b"GPUs: 2" in two.stderr
+
+
+def _rank(rank, world, port, backend, ndev, q):
+    sys.path.insert(0, ROOT)
+    import torch
+    import torch.distributed as dist
+    import msk144cudecoder_b200 as m
+    from msk144cudecoder_b200 import synth
+    from msk144cudecoder_b200.sharding import decode_sharded_batch
+    dev = rank % ndev
+    torch.cuda.set_device(dev)
+    dist.init_process_group(backend, init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world,
+                            **({"device_id": torch.device("cuda", dev)} if backend == "nccl" else {}))
+    with m.Decoder(device=dev, compat_cache=True, **KW) as d:
+        def decode_channels(chans):
+            x = np.stack([synth.cfg5_channel(c, seconds=SECONDS)[0] for c in chans])
+            return d.decode_host(x, nchan=len(chans))[0]
+        lines = decode_sharded_batch(decode_channels, NCHAN, rank, world)
+    dist.barrier()
+    dist.destroy_process_group()
+    q.put((rank, strip(lines)))
+
+
+@pytest.mark.gpu
+def test_two_ranks_gather_equals_single_gpu(gpu, synth):
+    """sharding.decode_sharded_batch with the CUDA decoder on every rank: rank 0's merged lines == one decoder's."""
+    import torch
+    import torch.multiprocessing as mp
+    ndev = torch.cuda.device_count()
+    backend = "nccl" if ndev >= 2 else "gloo"
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_rank, args=(r, 2, port, backend, ndev, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=600) for _ in range(2))
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        single, _ = d.decode_host(channels(synth), nchan=NCHAN)
+    key = lambda ls: sorted(ls, key=lambda t: (t[0], t[1], t[2]))
+    assert got[0] == key(strip(single)) and len(got[0]) > 0
+    assert set(got[1]) < set(got[0])           # rank 1 keeps only its own share

@@ -28,7 +28,7 @@ def gpu(product):
 
 def test_frontend_method2_matches_oracle(gpu, orc, synth):
     x, _ = synth.cfg1_demo(seconds=3.0, seed=2)
-    with gpu.Decoder(width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, width=20, depth=1) as d:
         blocks, powers = d.frontend(x)
     assert blocks.shape[0] == synth.num_blocks(len(x))
     for k in range(blocks.shape[0]):
@@ -41,7 +41,7 @@ def test_frontend_method2_matches_oracle(gpu, orc, synth):
 
 def test_frontend_iq_matches_oracle(gpu, orc, synth):
     iq, _ = synth.cfg3_deep_iq(seconds=2.0, seed=5)
-    with gpu.Decoder(read_mode=2, width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, read_mode=2, width=20, depth=1) as d:
         blocks, powers = d.frontend(iq)
     for k in range(blocks.shape[0]):
         ref = orc.frontend_iq(iq[2 * k * 2592:2 * (k * 2592 + 5184)])
@@ -51,7 +51,7 @@ def test_frontend_iq_matches_oracle(gpu, orc, synth):
 
 def test_frontend_fft_matches_oracle(gpu, orc, synth):
     x, _ = synth.cfg1_demo(seconds=2.0, seed=3)
-    with gpu.Decoder(method=1, width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, method=1, width=20, depth=1) as d:
         blocks, _ = d.frontend(x)
     for k in range(blocks.shape[0]):
         ref = orc.frontend_audio(x[k * 2592:k * 2592 + 5184], 1)
@@ -65,7 +65,7 @@ def test_scan_softbits_match_oracle(gpu, orc, synth, depth, thr):
     blk = orc.frontend_audio(x[:5184])
     cfg = orc.config(width=60, step=2, depth=depth, thr=thr, scan_mode=1, nthreads=8)
     ref = orc.decode_block(blk, cfg)
-    with gpu.Decoder(width=60, step=2, depth=depth, thr=thr) as d:
+    with gpu.Decoder(compat_cache=True, width=60, step=2, depth=depth, thr=thr) as d:
         cands, llr, llr_item = d.scan(blk[None, :])
     cands = cands[0]
     assert len(cands) == len(ref)
@@ -107,7 +107,7 @@ def test_ldpc_matches_oracle(gpu, orc, synth):
     extra.append(z)
     llr_all = np.concatenate([llr] + extra)
     fo, mo, io, no = orc.ldpc_decode_batch(llr_all, nthreads=8)
-    with gpu.Decoder(width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, width=20, depth=1) as d:
         fg, mg, ig, ng = d.ldpc_decode(llr_all)
     flag_mismatch = int((fo != fg).sum())
     both = fo & fg
@@ -125,7 +125,7 @@ def test_stream_lines_match_oracle(gpu, orc, synth):
     x, pings = synth.cfg1_demo(seconds=20.0, seed=1)
     cfg = orc.config(width=100, step=2, depth=3, thr=1, nthreads=8)
     ref, nb = orc.decode_stream(x, cfg)
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1, max_batch_blocks=16) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1, max_batch_blocks=16) as d:
         lines, results = d.decode_host(x)
         st = d.stage_times()
     assert st["blocks"] == nb and st["kernel_launches"] >= 3 * ((nb + 15) // 16)
@@ -134,7 +134,7 @@ def test_stream_lines_match_oracle(gpu, orc, synth):
     for r in results:
         assert gpu.decode_message(r["message"][:77]) in {p.text for p in pings}
     # batch size must not change anything (launch grouping is invisible)
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1, max_batch_blocks=5) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1, max_batch_blocks=5) as d:
         lines2, results2 = d.decode_host(x)
     assert lines_key(lines2) == lines_key(lines)
     assert np.array_equal(np.sort(results2, order=["block_index", "item_index"]),
@@ -145,14 +145,14 @@ def test_iq_deep_stream_matches_oracle(gpu, orc, synth):
     iq, pings = synth.cfg3_deep_iq(seconds=5.0, seed=145, npings=4)
     cfg = orc.config(center=0.0, width=500, step=1, depth=6, thr=3, read_mode=2, nthreads=8)
     ref, nb = orc.decode_stream(iq, cfg, max_blocks=6)
-    with gpu.Decoder(center=0.0, width=500, step=1, depth=6, thr=3, read_mode=2) as d:
+    with gpu.Decoder(compat_cache=True, center=0.0, width=500, step=1, depth=6, thr=3, read_mode=2) as d:
         lines, _ = d.decode_host(iq[: 2 * (5 * 2592 + 5184)])
     assert lines_key(lines) == lines_key(ref)
 
 
 def test_push_poll_equals_batch(gpu, synth):
     x, _ = synth.cfg1_demo(seconds=10.0, seed=4)
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1) as d:
         batch, _ = d.decode_host(x)
         raw = x.tobytes()
         got = []
@@ -168,7 +168,7 @@ def test_push_poll_equals_batch(gpu, synth):
 
 def test_multichannel_equals_per_channel(gpu, synth):
     chans = [synth.cfg5_channel(c, seconds=4.0)[0] for c in range(3)]
-    with gpu.Decoder(width=100, step=2, depth=3, thr=2) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=2) as d:
         per = []
         for c, x in enumerate(chans):
             l, _ = d.decode_host(x)
@@ -180,7 +180,7 @@ def test_multichannel_equals_per_channel(gpu, synth):
 
 def test_cli_matches_library(gpu, synth, tmp_path):
     x, _ = synth.cfg1_demo(seconds=8.0, seed=1)
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1) as d:
         lines, _ = d.decode_host(x)
     p = subprocess.run([gpu.CLI_PATH, "--search-width=100", "--scan-depth=3"], input=x.tobytes(), capture_output=True)
     assert p.returncode == 0
@@ -194,7 +194,7 @@ def test_cli_matches_library(gpu, synth, tmp_path):
 
 
 def test_empty_and_short_inputs(gpu):
-    with gpu.Decoder(width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, width=20, depth=1) as d:
         assert d.decode_host(np.zeros(5183, np.int16))[0] == []
         lines, res = d.decode_host(np.zeros(5184, np.int16))     # all-zero block: rms 0 -> NaNs, no decode, no crash
         assert lines == [] and len(res) == 0
@@ -242,9 +242,9 @@ def test_push_skips_wav_header_when_asked(gpu, synth):
     raw = x.tobytes()
     hdr = b"RIFF" + struct.pack("<I", 36 + len(raw)) + b"WAVE" + b"fmt " + struct.pack("<I", 16) + \
         struct.pack("<HHIIHH", 1, 1, 12000, 24000, 2, 16) + b"data" + struct.pack("<I", len(raw))
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1) as d:
         want, _ = d.decode_host(x)
-    with gpu.Decoder(width=100, step=2, depth=3, thr=1, flags=gpu.FLAG_SKIP_WAV_HEADER) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=1, flags=gpu.FLAG_SKIP_WAV_HEADER) as d:
         got = []
         data = hdr + raw
         for i in range(0, 70, 7):               # the header arrives in fragments
@@ -259,11 +259,11 @@ def test_twin_sharing_is_invisible(gpu, synth, monkeypatch):
     decodes one of the two and reports both.  Every LDPC success record must be the same with the sharing off."""
     x, _ = synth.cfg2_deep_audio(seconds=12.0, seed=144, npings=24)
     kw = dict(center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
-    with gpu.Decoder(**kw) as d:
+    with gpu.Decoder(compat_cache=True, **kw) as d:
         lines, res = d.decode_host(x, result_cap=1 << 18)
         ncw = d.stage_times()["llr_codewords"]
     monkeypatch.setenv("MSK144_NO_TWINS", "1")
-    with gpu.Decoder(**kw) as d:
+    with gpu.Decoder(compat_cache=True, **kw) as d:
         lines0, res0 = d.decode_host(x, result_cap=1 << 18)
         ncw0 = d.stage_times()["llr_codewords"]
     order = ["block_index", "item_index"]
@@ -282,7 +282,7 @@ def test_deinterleave_is_a_transpose(gpu, nchan, nsamp):
     xin = torch.from_numpy(x).cuda()
     out = torch.full((nchan, nsamp), 12345, dtype=torch.int16, device="cuda")
     torch.cuda.synchronize()
-    with gpu.Decoder(width=20, depth=1) as d:
+    with gpu.Decoder(compat_cache=True, width=20, depth=1) as d:
         d.deinterleave_device(xin.data_ptr(), out.data_ptr(), nsamp, nchan)
         torch.cuda.synchronize()
     assert np.array_equal(out.cpu().numpy(), x.T)
@@ -292,7 +292,7 @@ def test_interleaved_input_equals_channel_major(gpu, synth):
     chans = [synth.cfg5_channel(c, seconds=4.0)[0] for c in range(5)]
     cm = np.concatenate(chans)
     il = np.stack(chans, axis=1).copy()                    # [t][c]
-    with gpu.Decoder(width=100, step=2, depth=3, thr=2) as d:
+    with gpu.Decoder(compat_cache=True, width=100, step=2, depth=3, thr=2) as d:
         a, ra = d.decode_host(cm, nchan=5)
         b, rb = d.decode_host(il, nchan=5, interleaved=True)
     assert len(a) > 0 and a == b
@@ -308,10 +308,10 @@ def test_multichannel_streaming_equals_single_channel_streams(gpu, synth):
     kw = dict(width=100, step=2, depth=3, thr=2)
     want = []
     for c in range(nch):
-        with gpu.Decoder(**kw) as d:
+        with gpu.Decoder(compat_cache=True, **kw) as d:
             d.push(chans[c].tobytes())
             want += [dict(l, channel=c) for l in d.poll(4096)]
-    with gpu.Decoder(**kw) as d:
+    with gpu.Decoder(compat_cache=True, **kw) as d:
         got, i, rng = [], 0, np.random.default_rng(1)
         while i < len(il):
             n = int(rng.integers(1, 60000))

@@ -11,14 +11,24 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 
 
 def test_partitions():
-    from msk144cudecoder_b200.sharding import channels_of_rank, time_chunks
+    from msk144cudecoder_b200.sharding import channels_of_rank
     for n in (0, 1, 7, 8, 1024):
         for w in (1, 2, 4, 8):
             parts = [channels_of_rank(n, r, w) for r in range(w)]
             assert sorted(sum(parts, [])) == list(range(n))
             assert max(map(len, parts)) - min(map(len, parts)) <= 1
-    ch = time_chunks(4165, 8)
-    assert [c.start for c in ch][0] == 0 and ch[-1].stop == 4165 and sum(len(c) for c in ch) == 4165
+
+
+def test_batch_form_maps_local_channels_back():
+    from msk144cudecoder_b200.sharding import decode_sharded_batch
+    seen = []
+
+    def decode_channels(chans):
+        seen.append(list(chans))
+        return [dict(channel=i, block=0, text=f"c{c}") for i, c in enumerate(chans)]
+
+    out = decode_sharded_batch(decode_channels, 7, 1, 3, gather=False)
+    assert seen == [[3, 4]] and [(l["channel"], l["text"]) for l in out] == [(3, "c3"), (4, "c4")]
 
 
 def _worker(rank, world, port, q):

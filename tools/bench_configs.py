@@ -39,7 +39,7 @@ def stream_bench(name, x, pings, per_sample, reps=3, **kw):
     nb = synth.num_blocks(nsamp)
     xp = torch.from_numpy(x).pin_memory()
     xd = xp.to(dev)
-    with m.Decoder(max_batch_blocks=128, **kw) as d:
+    with m.Decoder(compat_cache=True, max_batch_blocks=128, **kw) as d:
         s = torch.cuda.Stream(dev)
         d.run_device(xd.data_ptr(), nsamp, 1, s.cuda_stream)
         torch.cuda.synchronize()
@@ -85,7 +85,7 @@ def cfg4():
     g = torch.Generator(device=dev).manual_seed(146)
     peak = hbm_peak()
     tot_ms, rows = 0.0, []
-    with m.Decoder(width=20, depth=1) as d:
+    with m.Decoder(compat_cache=True, width=20, depth=1) as d:
         s = torch.cuda.Stream(dev)
         out = torch.empty((per_point, 4), dtype=torch.int32, device=dev)
         flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
@@ -135,7 +135,7 @@ def cfg5(nchan=1024, seconds=60.0):
     x = torch.from_numpy(np.concatenate(chans)).pin_memory()
     gen_s = time.perf_counter() - t0
     nb = synth.num_blocks(len(chans[0])) * nchan
-    with m.Decoder(center=1500.0, max_batch_blocks=128, **DEEP) as d:
+    with m.Decoder(compat_cache=True, center=1500.0, max_batch_blocks=128, **DEEP) as d:
         d.decode_host(x.numpy()[: len(chans[0]) * 8], nchan=8, line_cap=1 << 12, result_cap=0)   # warm-up
         t0 = time.perf_counter()
         lines, _ = d.decode_host(x.numpy(), nchan=nchan, line_cap=1 << 19, result_cap=0)
@@ -155,7 +155,7 @@ def deinterleave(nchan=1024, nsamp=720000, reps=20):
     dev = torch.device("cuda", 0)
     x = torch.randint(-30000, 30000, (nsamp, nchan), dtype=torch.int16, device=dev)
     out = torch.empty((nchan, nsamp), dtype=torch.int16, device=dev)
-    with m.Decoder(width=20, depth=1) as d:
+    with m.Decoder(compat_cache=True, width=20, depth=1) as d:
         s = torch.cuda.Stream(dev)
         torch.cuda.synchronize()
         d.deinterleave_device(x.data_ptr(), out.data_ptr(), nsamp, nchan, s.cuda_stream)
@@ -179,7 +179,7 @@ def latency(seconds=30.0):
     raw = x.tobytes()
     hop = 2592 * 2
     for name, kw in (("deep", dict(center=1500.0, **DEEP)), ("default", dict(width=100.0, step=2.0, depth=3, thr=1))):
-        with m.Decoder(max_batch_blocks=8, **kw) as d:
+        with m.Decoder(compat_cache=True, max_batch_blocks=8, **kw) as d:
             d.push(raw[: 5184 * 2])
             d.poll()
             ts = []

@@ -34,7 +34,7 @@ def main():
     which = sys.argv[1:] or ["ldpc", "scan"]
     dev = torch.device("cuda", 0)
     if "ldpc" in which:
-        dec = m.Decoder(width=20, depth=1)
+        dec = m.Decoder(compat_cache=True, width=20, depth=1)
         n = 1 << 21
         out = torch.empty((n, 4), dtype=torch.int32, device=dev)
         g = torch.Generator(device=dev).manual_seed(1)
@@ -58,7 +58,7 @@ def main():
         xd = torch.from_numpy(x).to(dev)
         for name, kw in [("deep", dict(center=1500.0, width=500.0, step=1.0, depth=6, thr=3)),
                          ("cfg1", dict(center=1500.0, width=100.0, step=2.0, depth=3, thr=1))]:
-            dec = m.Decoder(max_batch_blocks=128, **kw)
+            dec = m.Decoder(compat_cache=True, max_batch_blocks=128, **kw)
             s = torch.cuda.Stream()
             for _ in range(2):
                 nb = dec.run_device(xd.data_ptr(), len(x), 1, s.cuda_stream)

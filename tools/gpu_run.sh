@@ -10,9 +10,10 @@ for step in "$@"; do
     smoke)  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" ;;
     tests)  timeout 1500 python -m pytest tests -m gpu -q -x --timeout=900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -30 gpurun_out/pytest_gpu.log ;;
     testsall) timeout 1500 python -m pytest tests -m gpu -q --timeout=900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -60 gpurun_out/pytest_gpu.log ;;
+    golden60) timeout 900 python tools/make_golden.py gpurun_out/golden audio_deep_60s iq_deep_60s > gpurun_out/golden60.log 2>&1; echo "golden60 rc=$?"; tail -4 gpurun_out/golden60.log; cp gpurun_out/golden/*_60s.npz tests/golden/ ;;
     golden) timeout 900 python tools/make_golden.py gpurun_out/golden > gpurun_out/golden.log 2>&1; echo "golden rc=$?"; tail -12 gpurun_out/golden.log ;;
     bench)  timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.log; tail -5 gpurun_out/bench.err ;;
-    benchref) timeout 900 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_ref.log 2> gpurun_out/bench_ref.err; echo "benchref rc=$?"; tail -3 gpurun_out/bench_ref.log; tail -5 gpurun_out/bench_ref.err ;;
+    benchref) timeout 1200 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.log 2> gpurun_out/bench_ref.err; echo "benchref rc=$?"; tail -3 gpurun_out/bench_ref.log; tail -5 gpurun_out/bench_ref.err ;;
     configs) timeout 1200 python tools/bench_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"; cut -c1-600 gpurun_out/configs.jsonl; tail -5 gpurun_out/configs.err ;;
     fullsize) timeout 1500 python -m pytest tests/test_gpu_fullsize.py -m gpu -q --timeout=900 > gpurun_out/pytest_fullsize.log 2>&1; echo "fullsize rc=$?"; tail -40 gpurun_out/pytest_fullsize.log ;;
     stages) timeout 600 python tools/bench_stages.py > gpurun_out/stages.log 2>&1; echo "stages rc=$?"; cat gpurun_out/stages.log | cut -c1-400 ;;

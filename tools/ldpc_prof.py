@@ -10,7 +10,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import msk144cudecoder_b200 as m  # noqa: E402
 
-dec = m.Decoder(width=20, depth=1)
+dec = m.Decoder(compat_cache=True, width=20, depth=1)
 n = 1 << 21
 dev = torch.device("cuda", 0)
 out = torch.empty((n, 4), dtype=torch.int32, device=dev)

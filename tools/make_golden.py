@@ -43,6 +43,57 @@ CASES = {
     "audio_deep": dict(gen=lambda: synth.cfg2_deep_audio(seconds=1.4, seed=144, npings=2)[0], read_mode=1, method=2,
                        center=1500.0, width=500.0, step=1.0, depth=6, thr=3, llr_blocks=[0], block_dump=[0], llr_subset=800),
 }
+# The headline configurations at length: the first 60 s (276 blocks) of BASELINE.json's cfg2 / cfg3 streams -- the very
+# prefix bench.py's reference arm decodes.  "compact" fixtures: CLI lines, per-block SNR, every decoded item (payload,
+# position, iterations) and the per-block count of sync-gated candidates; no per-candidate arrays (15 MB per block).
+LONG_SECONDS = 60.0
+LONG_CASES = {
+    "audio_deep_60s": dict(gen=lambda: synth.cfg2_deep_audio(seconds=900.0, seed=144)[0][: int(LONG_SECONDS * 12000)],
+                           read_mode=1, method=2, center=1500.0, width=500.0, step=1.0, depth=6, thr=3),
+    "iq_deep_60s": dict(gen=lambda: synth.cfg3_deep_iq(seconds=900.0, seed=145)[0][: 2 * int(LONG_SECONDS * 12000)],
+                        read_mode=2, method=2, center=0.0, width=500.0, step=1.0, depth=6, thr=3),
+}
+PRESENT_DTYPE = np.dtype([("block", "<i4"), ("item", "<i4"), ("pos", "<u4"), ("f0", "<f4"), ("nbadsync", "<i4"),
+                          ("xb", "<f4"), ("num_avg", "<i4"), ("iters", "<i4"), ("nhard", "<i4"), ("pad", "<i4"),
+                          ("message", "u1", (80,))])
+assert PRESENT_DTYPE.itemsize == 120
+
+
+def ref_cli(c):
+    return [os.path.join(REF, "msk144cudecoder_ref"), f"--search-width={c['width']}", f"--search-step={c['step']}",
+            f"--scan-depth={c['depth']}", f"--nbadsync-threshold={c['thr']}", f"--read-mode={c['read_mode']}",
+            f"--analytic-method={c['method']}", f"--center-frequency={c['center']}"]
+
+
+def mask_date(text):
+    return [re.sub(r"date=\d{14}", "date=" + "x" * 14, l) for l in text.splitlines()]
+
+
+def run_long_case(name, c, outdir):
+    raw = np.ascontiguousarray(c["gen"]())
+    with tempfile.TemporaryDirectory() as td:
+        inp = os.path.join(td, "in.raw")
+        raw.tofile(inp)
+        prefix = os.path.join(td, "d")
+        subprocess.run([os.path.join(REF, "ref_dump"), "stream", str(c["read_mode"]), str(c["method"]), str(c["center"]),
+                        str(c["width"]), str(c["step"]), str(c["depth"]), str(c["thr"]), inp, prefix, "0", "compact"], check=True)
+        pres = np.fromfile(prefix + ".present.bin", PRESENT_DTYPE)
+        snr = np.fromfile(prefix + ".snr.i32", np.int32)
+        ngated = np.fromfile(prefix + ".ngated.i32", np.int32)
+        tagged = [l.split("\t", 1) for l in open(prefix + ".lines.txt").read().splitlines()]
+        p = subprocess.run(ref_cli(c), input=raw.tobytes(), capture_output=True, check=True)
+        lines = mask_date(p.stdout.decode())
+    out = os.path.join(outdir, name + ".npz")
+    np.savez_compressed(
+        out, read_mode=c["read_mode"], method=c["method"], center=c["center"], width=c["width"], step=c["step"],
+        depth=c["depth"], thr=c["thr"], nblocks=len(snr), snr=snr.astype(np.int8), ngated=ngated,
+        block=pres["block"].astype(np.int16), item=pres["item"], pos=pres["pos"].astype(np.uint16), f0=pres["f0"],
+        nbadsync=pres["nbadsync"].astype(np.int8), xb=pres["xb"], iters=pres["iters"].astype(np.int8),
+        nhard=pres["nhard"].astype(np.int8), msg=np.packbits(pres["message"], axis=-1), cli_lines=np.array(lines),
+        line_block=np.array([int(t[0]) for t in tagged], np.int32), line_text=np.array([t[1] for t in tagged]))
+    assert [t[1] for t in tagged] + ["Done"] == lines, "reference CLI stdout != reference do_decode + ResultFilter lines"
+    print(f"{name}: {len(snr)} blocks, {len(pres)} decoded items, {int(ngated.sum())} gated candidates, "
+          f"{len(lines)} cli lines, {os.path.getsize(out) / 1e6:.2f} MB")
 
 
 def run_case(name, c, outdir):
@@ -122,3 +173,6 @@ if __name__ == "__main__":
             run_case(name, c, outdir)
     if not only or "ldpc" in only:
         run_ldpc(outdir)
+    for name, c in LONG_CASES.items():
+        if not only or name in only:
+            run_long_case(name, c, outdir)

@@ -13,7 +13,7 @@ from msk144cudecoder_b200 import synth  # noqa: E402
 
 x, _ = synth.cfg2_deep_audio(seconds=60.0, seed=144)
 xd = torch.from_numpy(x).to("cuda:0")
-dec = m.Decoder(max_batch_blocks=128, center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
+dec = m.Decoder(compat_cache=True, max_batch_blocks=128, center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
 s = torch.cuda.Stream()
 L = m.lib()
 out = (C.c_ulonglong * 16)()
