@@ -126,6 +126,19 @@ def mask_date(text):
     return [re.sub(r"date=\d{14}", "date=" + "x" * 14, l) for l in text.splitlines()]
 
 
+def untie(lines):
+    """Lines without f0 / pattern_idx: they name the winner among candidates tied in (num_avg, nbadsync), which the
+    reference does not reproduce from one run to the next (its LLR race decides which marginal candidates decode, its
+    unstable sort then picks)."""
+    return [re.sub(r"f0=[^;]*; ", "", re.sub(r"pattern_idx=\d+; ", "", l)) for l in lines]
+
+
+def compare_lines(a, b):
+    """{identical: same text/snr/num_avg/nbadsync/order in every line, strict: lines equal in every field, of: lines}"""
+    same = untie(a) == untie(b)
+    return {"identical": same, "strict": sum(x == y for x, y in zip(a, b)) - 1 if same else None, "of": len(b) - 1}
+
+
 def cli_once(cmd, data, timeout=1800):
     """One process: bytes on stdin, stdout captured.  Returns (wall seconds, masked stdout lines)."""
     env = dict(os.environ, LD_LIBRARY_PATH="/usr/local/cuda/lib64:" + os.environ.get("LD_LIBRARY_PATH", ""))
@@ -143,16 +156,20 @@ def cli_figures(cmd, sample, full, steps, warmup, audio_s_sample, audio_s_full):
     step (median), one pass over the whole stream.  Steady-state = start-up subtracted."""
     one_block = sample[: 5184 * 2]
     startup = float(np.median([cli_once(cmd, one_block)[0] for _ in range(3)]))
-    times, lines = [], None
+    times, lines, strict_same = [], None, 0
     for i in range(warmup + steps):
         dt, ls = cli_once(cmd, sample)
-        if lines is not None and ls != lines:
-            raise RuntimeError("output differs between two runs on the same input")
-        lines = ls
+        if lines is not None:
+            if untie(ls) != untie(lines):
+                raise RuntimeError("output differs between two runs on the same input beyond f0 / pattern_idx tie-breaks")
+            strict_same += ls == lines
+        else:
+            lines = ls
         if i >= warmup:
             times.append(dt)
     dt_med = float(np.median(times))
     out = {"startup_s": startup, "sample_s_median": dt_med, "sample_s_all": [round(t, 4) for t in times],
+           "runs_with_strictly_identical_output": f"{strict_same} of {warmup + steps - 1} repeats (all identical apart from f0 / pattern_idx tie-breaks)",
            "raw_value": audio_s_sample / dt_med, "value": audio_s_sample / max(1e-9, dt_med - startup), "unit": UNIT,
            "sample": f"first {int(round(audio_s_sample / 0.216))} blocks ({audio_s_sample:.1f} s of audio) per process, "
                      "bytes on stdin, lines on stdout; value = steady state (start-up on a one-block input subtracted), "
@@ -201,8 +218,9 @@ def run_reference(args, rank):
             gl = golden_lines()
             extra = {"cli": fig, "raw_value": fig["raw_value"], "startup_s": fig["startup_s"],
                      "full_stream_value": fig.get("full_stream_value"),
-                     "lines_sha16": lines_digest(lines), "lines": len(lines) - 1,
-                     "lines_identical_to_golden": (lines == gl) if gl is not None and args.seconds >= SAMPLE_SECONDS else None}
+                     "lines_sha16": lines_digest(untie(lines)), "lines": len(lines) - 1,
+                     "lines_vs_golden": compare_lines(lines, gl) if gl is not None and args.seconds >= SAMPLE_SECONDS else None}
+            extra["lines_identical_to_golden"] = extra["lines_vs_golden"]["identical"] if extra["lines_vs_golden"] else None
             note = ("unmodified reference CLI (its CUDA kernels recompiled for sm_100a, no fast-math) on the same B200; one process "
                     "per step, median; value = steady state: the process start-up (CUDA context, cuFFT plan; measured on a one-block "
                     f"input: {fig['startup_s']:.2f} s) is subtracted, raw_value keeps it")
@@ -479,18 +497,23 @@ def main():
                                              synth.num_blocks(ns) * 0.216, audio_s)
                 line["cli"] = fig
                 check = {"sample": f"first {synth.num_blocks(ns)} blocks of the stream through both executables, stdout compared "
-                                   "line by line (date masked)", "ours_lines": len(cli_lines) - 1, "ours_sha16": lines_digest(cli_lines)}
+                                   "line by line (date masked)", "ours_lines": len(cli_lines) - 1, "ours_sha16": lines_digest(untie(cli_lines))}
                 gl = golden_lines()
+                check["criterion"] = ("identical = every line equal in text, snr, num_avg, nbadsync and order; f0 / pattern_idx are a "
+                                      "tie-break the reference itself does not reproduce between two runs (strict = lines equal in "
+                                      "those two fields as well)")
                 if gl is not None and args.seconds >= SAMPLE_SECONDS:
-                    check["golden"] = cli_lines == gl          # committed output of the reference (tests/golden)
+                    check["golden"] = compare_lines(cli_lines, gl)   # committed output of the reference (tests/golden)
                 if os.path.exists(REF_EXE):
                     try:
                         _, ref_lines = cli_once([REF_EXE] + CLI_FLAGS, sample)   # the checker, outside every timed region
-                        check["live"] = cli_lines == ref_lines
-                        check["reference_lines"], check["reference_sha16"] = len(ref_lines) - 1, lines_digest(ref_lines)
+                        check["live"] = compare_lines(cli_lines, ref_lines)
+                        _, ref_again = cli_once([REF_EXE] + CLI_FLAGS, sample)
+                        check["reference_vs_itself"] = compare_lines(ref_again, ref_lines)
+                        check["reference_lines"], check["reference_sha16"] = len(ref_lines) - 1, lines_digest(untie(ref_lines))
                     except Exception as e:  # noqa: BLE001
                         check["live_error"] = " ".join(str(e).split())[:160]
-                verdicts = [check[k] for k in ("golden", "live") if k in check]
+                verdicts = [check[k]["identical"] for k in ("golden", "live") if k in check]
                 line["lines_identical_to_reference"] = all(verdicts) if verdicts else None
                 line["reference_check"] = check
             except Exception as e:  # noqa: BLE001

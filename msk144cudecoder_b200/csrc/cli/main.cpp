@@ -10,6 +10,10 @@
 
 #include <algorithm>
 #include <chrono>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
+#include <cerrno>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -180,16 +184,47 @@ int main(int argc, char* const argv[]) {
             for (size_t i = 0; i < ne; i++) print_line(events[i].best);
         } while (ne == events.size());
     };
-    while (true) {
-        // read() returns what is available: real-time input is processed block by block, a file or a
-        // fast pipe is processed in large launch groups.
-        const ssize_t n = read(0, buf.data(), buf.size());
-        if (n < 0) {
-            perror("read");
-            rc_exit = 2;
-            break;
+    // stdin is drained by a reader thread while the GPU works on what has arrived so far: real-time input is processed
+    // hop by hop as it comes (one read = one push), a file or a fast pipe accumulates into large launch groups instead
+    // of being chopped into pipe-buffer sized pieces (a 64 KB pipe read is 12 blocks).
+    struct Inbox {
+        std::mutex m;
+        std::condition_variable cv;
+        std::vector<unsigned char> data;
+        bool eof = false;
+        int err = 0;
+    } inbox;
+    const size_t inbox_cap = std::max<size_t>(64u << 20, 4 * buf.size());  // back-pressure on a producer that outruns the GPU
+    std::thread reader([&] {
+        std::vector<unsigned char> tmp(1u << 20);
+        while (true) {
+            const ssize_t n = read(0, tmp.data(), tmp.size());
+            std::unique_lock<std::mutex> lk(inbox.m);
+            if (n <= 0) {
+                inbox.eof = true, inbox.err = n < 0 ? errno : 0;
+                inbox.cv.notify_all();
+                return;
+            }
+            inbox.cv.wait(lk, [&] { return inbox.data.size() < inbox_cap; });
+            inbox.data.insert(inbox.data.end(), tmp.data(), tmp.data() + n);
+            inbox.cv.notify_all();
         }
-        if (n == 0) break;
+    });
+    while (true) {
+        buf.clear();
+        {
+            std::unique_lock<std::mutex> lk(inbox.m);
+            inbox.cv.wait(lk, [&] { return !inbox.data.empty() || inbox.eof; });
+            buf.swap(inbox.data);
+            if (buf.empty() && inbox.err) {
+                errno = inbox.err;
+                perror("read");
+                rc_exit = 2;
+            }
+            inbox.cv.notify_all();
+        }
+        if (buf.empty()) break;
+        const ssize_t n = static_cast<ssize_t>(buf.size());
         total_bytes += static_cast<size_t>(n);
         const auto t0 = std::chrono::steady_clock::now();
         const int64_t before = 0;
@@ -229,6 +264,12 @@ int main(int argc, char* const argv[]) {
             std::cerr << "Warning: Working loop takes too much time: " << ms << " ms"
                       << " of " << 210.0 * blocks_in << " ms max." << std::endl;
     }
+    if (rc_exit != 0) {  // error: the reader may sit in read() for ever; leave without joining it
+        std::cout.flush();
+        std::cerr.flush();
+        _exit(rc_exit);
+    }
+    reader.join();
     // main.cu:274-278,289-293: the final short fread ends the loop
     size_t leftover;
     if (total_bytes < block_bytes) leftover = total_bytes;

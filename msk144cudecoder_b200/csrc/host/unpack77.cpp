@@ -192,6 +192,10 @@ bool unpack28(int n28, std::string* out) {
             s += C4[i5];
             s += C4[i6];
             c13 = ltrim(s);
+            // the protocol's work-arounds for two prefixes that do not fit the 6-character pattern (the packer maps
+            // 3DA0xxx -> 3D0xxx and 3Xa... -> Qa...; undone here)
+            if (c13.compare(0, 3, "3D0") == 0 && c13.size() > 3 && c13[3] != ' ') c13 = "3DA0" + c13.substr(3);
+            else if (c13.size() > 1 && c13[0] == 'Q' && c13[1] >= 'A' && c13[1] <= 'Z') c13 = "3X" + c13.substr(1);
         }
     }
     c13 = rtrim(c13);

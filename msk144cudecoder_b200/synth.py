@@ -105,7 +105,38 @@ _A4 = " ABCDEFGHIJKLMNOPQRSTUVWXYZ"
 _FREE = " 0123456789ABCDEFGHIJKLMNOPQRSTUVWXYZ+-./?"
 
 
+_A38 = " 0123456789ABCDEFGHIJKLMNOPQRSTUVWXYZ/"
+
+
+def ihashcall(call: str, m: int) -> int:
+    """m-bit hash of a call sign (m = 10, 12, 22): base-38 value of the 11-character left-justified call times a
+    fixed multiplier, top m bits of the 64-bit product."""
+    c = call.strip("<>").ljust(11)[:11]
+    n8 = 0
+    for ch in c:
+        n8 = 38 * n8 + _A38.index(ch)
+    return ((47055833459 * n8) & 0xFFFFFFFFFFFFFFFF) >> (64 - m)
+
+
+def is_standard_call(c: str) -> bool:
+    """One or two leading characters (at most one of them a digit in front position), a digit, up to three letters."""
+    if len(c) >= 3 and c[2].isdigit():
+        c6 = c
+    elif len(c) >= 2 and c[1].isdigit():
+        c6 = " " + c
+    else:
+        return False
+    if len(c6) > 6:
+        return False
+    c6 = c6.ljust(6)
+    if not (c6[0] in _A1 and c6[1] in _A2 and c6[2] in _A3 and all(ch in _A4 for ch in c6[3:])):
+        return False
+    return " " not in c6.strip() and c6[1] != " "
+
+
 def pack28(call: str) -> int:
+    """28-bit field: tokens DE / QRZ / CQ / `CQ nnn` / `CQ xxxx` (written with an underscore or a blank), a hashed call
+    `<CALL>` (22-bit hash), or a standard call (with the 3DA0 / 3X work-arounds of the protocol)."""
     if call == "DE":
         return 0
     if call == "QRZ":
@@ -113,15 +144,25 @@ def pack28(call: str) -> int:
     if call == "CQ":
         return 2
     c = call.upper()
-    if len(c) >= 3 and c[2].isdigit():
-        c6 = c
-    elif len(c) >= 2 and c[1].isdigit():
-        c6 = " " + c
-    else:
+    if c.startswith("CQ_") or c.startswith("CQ "):
+        t = c[3:]
+        if t.isdigit() and len(t) == 3:
+            return 3 + int(t)
+        if t.isalpha() and 1 <= len(t) <= 4:
+            v = 0
+            for ch in t.rjust(4):
+                v = v * 27 + _A4.index(ch)
+            return 1003 + v
+        raise ValueError(f"bad CQ token: {call}")
+    if c.startswith("<") and c.endswith(">"):
+        return NTOKENS + ihashcall(c, 22)
+    if c.startswith("3DA0"):
+        c = "3D0" + c[4:]
+    elif c.startswith("3X") and len(c) > 2 and c[2].isalpha():
+        c = "Q" + c[2:]
+    if not is_standard_call(c):
         raise ValueError(f"not a standard call: {call}")
-    c6 = c6.ljust(6)
-    if len(c6) != 6:
-        raise ValueError(f"not a standard call: {call}")
+    c6 = (c if c[2].isdigit() and len(c) >= 3 else " " + c).ljust(6)
     i = [_A1.index(c6[0]), _A2.index(c6[1]), _A3.index(c6[2]), _A4.index(c6[3]), _A4.index(c6[4]),
          _A4.index(c6[5])]
     n = ((((i[0] * 36 + i[1]) * 10 + i[2]) * 27 + i[3]) * 27 + i[4]) * 27 + i[5]
@@ -132,10 +173,62 @@ def _to_bits(v: int, n: int) -> List[int]:
     return [(v >> (n - 1 - k)) & 1 for k in range(n)]
 
 
+def _grid4(t: str) -> Optional[int]:
+    if len(t) == 4 and t[:2].isalpha() and t[2:].isdigit() and t[0] <= "R" and t[1] <= "R":
+        return ((ord(t[0]) - 65) * 18 + (ord(t[1]) - 65)) * 100 + int(t[2:])
+    return None
+
+
+def _pack_type4(w: List[str]) -> Optional[List[int]]:
+    """`<HASHED> NONSTD [RRR|RR73|73]`, `NONSTD <HASHED> [...]`, `CQ NONSTD`: one call in full (up to 11 characters of
+    [0-9A-Z/]), the other as a 12-bit hash."""
+    rpt = {"": 0, "RRR": 1, "RR73": 2, "73": 3}
+    if len(w) == 2 and w[0] == "CQ" and 3 <= len(w[1]) <= 11 and all(ch in _A38[1:] for ch in w[1]):
+        full, n12, iflip, nrpt, icq = w[1], 0, 0, 0, 1
+    elif len(w) in (2, 3) and (len(w) == 2 or w[2] in rpt):
+        a, b = w[0], w[1]
+        if a.startswith("<") and not b.startswith("<"):
+            full, n12, iflip = b, ihashcall(a, 12), 0
+        elif b.startswith("<") and not a.startswith("<"):
+            full, n12, iflip = a, ihashcall(b, 12), 1
+        else:
+            return None
+        if not (3 <= len(full) <= 11 and all(ch in _A38[1:] for ch in full)):
+            return None
+        nrpt, icq = rpt[w[2] if len(w) == 3 else ""], 0
+    else:
+        return None
+    n58 = 0
+    for ch in full.rjust(11):
+        n58 = n58 * 38 + _A38.index(ch)
+    return _to_bits(n12, 12) + _to_bits(n58, 58) + [iflip] + _to_bits(nrpt, 2) + [icq] + _to_bits(4, 3)
+
+
+def _pack_type5(w: List[str]) -> Optional[List[int]]:
+    """EU VHF contest: `<CALL1> <CALL2> [R] RRSSSS GRID6` (report 52..59, serial 0..2047)."""
+    if len(w) not in (4, 5) or not (w[0].startswith("<") and w[1].startswith("<")):
+        return None
+    ir = 1 if w[2] == "R" else 0
+    if len(w) != 4 + ir:
+        return None
+    ex, g = w[2 + ir], w[3 + ir]
+    if not (len(ex) == 6 and ex.isdigit() and len(g) == 6 and g[:2].isalpha() and g[2:4].isdigit() and g[4:].isalpha()):
+        return None
+    irpt, iserial = int(ex[:2]) - 52, int(ex[2:])
+    if not (0 <= irpt <= 7 and iserial <= 2047 and g[0] <= "R" and g[1] <= "R" and g[4] <= "X" and g[5] <= "X"):
+        return None
+    ig = ((((ord(g[0]) - 65) * 18 + (ord(g[1]) - 65)) * 10 + int(g[2])) * 10 + int(g[3])) * 24 * 24 + (ord(g[4]) - 65) * 24 + (ord(g[5]) - 65)
+    return (_to_bits(ihashcall(w[0], 12), 12) + _to_bits(ihashcall(w[1], 22), 22) + [ir] + _to_bits(irpt, 3)
+            + _to_bits(iserial, 11) + _to_bits(ig, 25) + _to_bits(5, 3))
+
+
 def pack77(msg: str) -> np.ndarray:
-    """Pack a message into 77 bits.  Supports standard type-1 messages
-    (`CALL CALL GRID|[R]+-NN|RRR|RR73|73`, `CQ CALL GRID`), 18-hex-digit telemetry given as
-    `TLM:<hex>` and free text of up to 13 characters (anything else)."""
+    """Pack a message into 77 bits: every type the reference's gate admits (decode_softbits.cpp:30).
+      i3 = 1 / 2  `C1 C2 [R] GRID4 | [R]+-NN | RRR | RR73 | 73 | (nothing)`; C = DE, QRZ, CQ, `CQ nnn`, `CQ XXXX`,
+                  a standard call with optional /R (i3 = 1) or /P (i3 = 2), or a hashed call `<CALL>`
+      i3 = 4      one non-standard call in full + the other as `<CALL>` (12-bit hash), `CQ NONSTD`
+      i3 = 5      EU VHF contest, both calls hashed
+      0.5         telemetry, `TLM:<hex>` (71 bits);   0.0  free text of up to 13 characters (anything else)."""
     msg = msg.strip().upper()
     if msg.startswith("TLM:"):
         v = int(msg[4:], 16)
@@ -143,34 +236,59 @@ def pack77(msg: str) -> np.ndarray:
             raise ValueError("telemetry exceeds 71 bits")
         return np.array(_to_bits(v, 71) + _to_bits(5, 3) + _to_bits(0, 3), np.uint8)
     w = msg.split()
+    if len(w) >= 2 and w[0] == "CQ" and (w[1].isdigit() and len(w[1]) == 3 or w[1].isalpha() and len(w[1]) <= 4 and len(w) >= 3
+                                         and not is_standard_call(w[1])):
+        w = ["CQ_" + w[1]] + w[2:]          # directed CQ: the modifier belongs to the first field
+    b5 = _pack_type5(w)
+    if b5 is not None:
+        return np.array(b5, np.uint8)
     try:
-        if len(w) in (2, 3):
-            n28a, n28b = pack28(w[0]), pack28(w[1])
-            ir = 0
-            if len(w) == 2:
+        if len(w) in (2, 3, 4):
+            i3, ip = 1, [0, 0]
+            calls = []
+            for k in (0, 1):
+                c = w[k]
+                if c.endswith("/R") or c.endswith("/P"):
+                    if is_standard_call(c[:-2]):
+                        if c.endswith("/P"):
+                            i3 = 2
+                        ip[k], c = 1, c[:-2]
+                calls.append(c)
+            if "/P" in msg and "/R" in msg:
+                raise ValueError
+            n28a, n28b = pack28(calls[0]), pack28(calls[1])
+            ir, rest = 0, w[2:]
+            if len(rest) == 2:
+                if rest[0] != "R" or _grid4(rest[1]) is None:
+                    raise ValueError
+                ir, ig = 1, _grid4(rest[1])
+            elif len(rest) == 0:
                 ig = MAXGRID4 + 1
             else:
-                t = w[2]
+                t = rest[0]
                 if t == "RRR":
                     ig = MAXGRID4 + 2
                 elif t == "RR73":
                     ig = MAXGRID4 + 3
                 elif t == "73":
                     ig = MAXGRID4 + 4
-                elif len(t) == 4 and t[:2].isalpha() and t[2:].isdigit() and t[0] <= "R" and t[1] <= "R":
-                    ig = ((ord(t[0]) - 65) * 18 + (ord(t[1]) - 65)) * 100 + int(t[2:])
+                elif _grid4(t) is not None:
+                    ig = _grid4(t)
                 else:
                     if t[0] == "R":
                         ir, t = 1, t[1:]
                     snr = int(t)
-                    if not (t[0] in "+-" and -30 <= snr <= 49):
+                    if not (t[0] in "+-" and len(t) == 3 and -30 <= snr <= 49):
                         raise ValueError
                     ig = MAXGRID4 + 35 + snr
-            bits = (_to_bits(n28a, 28) + [0] + _to_bits(n28b, 28) + [0] + [ir] + _to_bits(ig, 15)
-                    + _to_bits(1, 3))
+            bits = (_to_bits(n28a, 28) + [ip[0]] + _to_bits(n28b, 28) + [ip[1]] + [ir] + _to_bits(ig, 15)
+                    + _to_bits(i3, 3))
             return np.array(bits, np.uint8)
     except (ValueError, IndexError):
         pass
+    b4 = _pack_type4(w)
+    if b4 is not None:
+        return np.array(b4, np.uint8)
     if len(msg) > 13 or any(ch not in _FREE for ch in msg):
         raise ValueError(f"cannot pack: {msg!r}")
     v = 0

@@ -33,15 +33,18 @@ def time_ldpc(dec, llr_dev, out_dev, n, reps=5):
 def main():
     which = sys.argv[1:] or ["ldpc", "scan"]
     dev = torch.device("cuda", 0)
-    if "ldpc" in which:
+    if "ldpc" in which or "noise" in which:
         dec = m.Decoder(compat_cache=True, width=20, depth=1)
         n = 1 << 21
         out = torch.empty((n, 4), dtype=torch.int32, device=dev)
         g = torch.Generator(device=dev).manual_seed(1)
         noise = torch.randn((n, 128), device=dev, generator=g) * 5.5     # LLR rms like the soft-bit stage
         ms = time_ldpc(dec, noise, out, n)
-        print(json.dumps({"bench": "ldpc_noise", "codewords": n, "ms": ms, "cw_per_s": n / ms * 1e3,
-                          "found": int((out[:, 2] < 0).sum().item())}), flush=True)
+        print(json.dumps({"bench": "ldpc_noise", "lib": os.path.basename(m.LIB_PATH), "form": "pair" if os.environ.get("MSK144_LDPC_NO_REFILL") else "stream",
+                          "codewords": n, "ms": ms, "cw_per_s": n / ms * 1e3,
+                          "found": int((out[:, 2] < 0).sum().item()),
+                          "out_sha": __import__("hashlib").sha256(out.cpu().numpy().tobytes()).hexdigest()[:12]}), flush=True)
+    if "ldpc" in which:
         base, msgs = synth.cfg4_llrs(1 << 15, 0.0, seed=146)
         for ebn0 in (0, 1, 2, 3, 4, 5, 6, 7):
             llr_h, _ = synth.cfg4_llrs(1 << 15, float(ebn0), seed=146 + ebn0)
@@ -67,7 +70,7 @@ def main():
             for _ in range(3):
                 dec.run_device(xd.data_ptr(), len(x), 1, s.cuda_stream)
             st = dec.stage_times()
-            print(json.dumps({"bench": "stages_" + name, "blocks": nb,
+            print(json.dumps({"bench": "stages_" + name, "lib": os.path.basename(m.LIB_PATH), "blocks": nb,
                               "us_per_block": {k: st[k] * 1e3 / st["blocks"] for k in ("frontend_ms", "scan_ms", "ldpc_ms", "total_ms")},
                               "rtf": 0.216 / (st["total_ms"] * 1e-3 / st["blocks"])}), flush=True)
             dec.close()

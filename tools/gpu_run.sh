@@ -9,7 +9,7 @@ for step in "$@"; do
     info)   nvidia-smi > gpurun_out/nvidia-smi.txt 2>&1; nproc >> gpurun_out/nvidia-smi.txt ;;
     smoke)  python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" ;;
     tests)  timeout 1500 python -m pytest tests -m gpu -q -x --timeout=900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -30 gpurun_out/pytest_gpu.log ;;
-    testsall) timeout 1500 python -m pytest tests -m gpu -q --timeout=900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -60 gpurun_out/pytest_gpu.log ;;
+    testsall) timeout 2400 python -m pytest tests -m gpu -q --timeout=900 > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -60 gpurun_out/pytest_gpu.log ;;
     golden60) timeout 900 python tools/make_golden.py gpurun_out/golden audio_deep_60s iq_deep_60s > gpurun_out/golden60.log 2>&1; echo "golden60 rc=$?"; tail -4 gpurun_out/golden60.log; cp gpurun_out/golden/*_60s.npz tests/golden/ ;;
     golden) timeout 900 python tools/make_golden.py gpurun_out/golden > gpurun_out/golden.log 2>&1; echo "golden rc=$?"; tail -12 gpurun_out/golden.log ;;
     bench)  timeout 900 python bench.py --steps 3 --warmup 3 > gpurun_out/bench.log 2> gpurun_out/bench.err; echo "bench rc=$?"; tail -3 gpurun_out/bench.log; tail -5 gpurun_out/bench.err ;;

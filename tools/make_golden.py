@@ -91,7 +91,14 @@ def run_long_case(name, c, outdir):
         nbadsync=pres["nbadsync"].astype(np.int8), xb=pres["xb"], iters=pres["iters"].astype(np.int8),
         nhard=pres["nhard"].astype(np.int8), msg=np.packbits(pres["message"], axis=-1), cli_lines=np.array(lines),
         line_block=np.array([int(t[0]) for t in tagged], np.int32), line_text=np.array([t[1] for t in tagged]))
-    assert [t[1] for t in tagged] + ["Done"] == lines, "reference CLI stdout != reference do_decode + ResultFilter lines"
+    # Two runs of the reference do not print the same f0 / pattern_idx everywhere: its LLRs carry a data race
+    # (sum_reduction.cuh:16 vs :32), so which marginal candidates decode varies, and ResultFilter's unstable sort then
+    # picks another winner among candidates tied in (num_avg, nbadsync).  Everything else must agree.
+    tie = lambda ls: [re.sub(r"f0=[^;]*; ", "", re.sub(r"pattern_idx=\d+; ", "", l)) for l in ls]
+    dump_lines = [t[1] for t in tagged] + ["Done"]
+    assert tie(dump_lines) == tie(lines), "reference CLI stdout != reference do_decode + ResultFilter lines (beyond tie-breaks)"
+    print(f"{name}: reference CLI vs reference do_decode run: {sum(a != b for a, b in zip(dump_lines, lines))} of {len(lines) - 1} "
+          "lines differ in f0 / pattern_idx (tie-break), none otherwise")
     print(f"{name}: {len(snr)} blocks, {len(pres)} decoded items, {int(ngated.sum())} gated candidates, "
           f"{len(lines)} cli lines, {os.path.getsize(out) / 1e6:.2f} MB")
 
