@@ -49,7 +49,14 @@ enum {
     /* Streaming surface only: if the pushed stream starts with a RIFF/WAVE header, skip to the first byte of
      * its "data" chunk instead of decoding the header as samples (the reference does the latter: README.md:62
      * pipes demo/0001.wav straight in).  Off by default for compatibility; the CLI sets it for --wav. */
-    MSK144_FLAG_SKIP_WAV_HEADER = 2
+    MSK144_FLAG_SKIP_WAV_HEADER = 2,
+    /* LDPC with the control flow of WSJT-X's bpdecode128_90 instead of the reference kernel's:
+     * iter = 0..10 (11 parity checks, the reference has 10: common.h:29, ldpc_kernel.cuh:161), the first hard decision
+     * that satisfies all parities and the CRC ends the decode (accepted if nharderror < 18), early stop when the number
+     * of unsatisfied checks has not decreased for three checks running (iter >= 5, more than 10 unsatisfied), optional
+     * a-priori mask (msk144_set_ap_mask).  Same arithmetic.  Off by default: the drop-in output is the reference's.
+     * bpdecode128_90.f90 is not on this box; the mode is restated from the published algorithm (parity unpinned). */
+    MSK144_FLAG_WSJTX_BP = 4
 };
 
 /* The seven CLI values of main.cu:124-133 + placement.  Zero-initialise, then msk144_config_defaults(). */
@@ -199,6 +206,10 @@ int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, u
 /* Same on device-resident LLRs, asynchronous on `stream`; d_out: [ncw] x 4 uint32 words
  * {bits 0..31, 32..63, 64..76 | found<<31, iters | nhard<<8}. */
 int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t ncw, uint32_t* d_out, void* stream);
+
+/* MSK144_FLAG_WSJTX_BP only: bits with apmask128[b] != 0 keep zn = llr in every iteration (bpdecode128_90's apmask;
+ * the caller puts its a-priori knowledge into their LLRs).  NULL clears the mask.  Applies to every later decode. */
+int msk144_set_ap_mask(msk144_decoder* dec, const uint8_t* apmask128);
 
 /* Device self-test of the LDPC kernel's packed math: all 2^32 float inputs through the f32x2 tanh and the
  * division-free platanh against libdevice tanhf and the reference's platanh (ldpc_kernel.cuh:65-93) with an

@@ -24,6 +24,7 @@ CLI_PATH = os.path.join(_HERE, "bin", "msk144cudecoder")
 BLOCK_SAMPLES, HOP_SAMPLES = 5184, 2592
 FLAG_COMPAT_DECODE_CACHE = 1
 FLAG_SKIP_WAV_HEADER = 2
+FLAG_WSJTX_BP = 4
 
 EXPORTED_SYMBOLS = [
     "msk144_last_error", "msk144_config_defaults", "msk144_create", "msk144_destroy", "msk144_get_info",
@@ -35,7 +36,7 @@ EXPORTED_SYMBOLS = [
     "msk144_aggregator_create", "msk144_aggregator_destroy", "msk144_aggregator_add", "msk144_aggregator_poll",
     "msk144_pool_last_error", "msk144_pool_create", "msk144_pool_destroy", "msk144_pool_size", "msk144_pool_member",
     "msk144_pool_decode_host", "msk144_pool_push_interleaved", "msk144_pool_poll", "msk144_pool_reset_stream",
-    "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math",
+    "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math", "msk144_set_ap_mask",
 ]
 
 
@@ -148,6 +149,7 @@ def lib():
         L.msk144_pool_reset_stream.argtypes = [vp]
         L.msk144_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double)]
         L.msk144_build_info.restype = C.c_char_p
+        L.msk144_set_ap_mask.argtypes = [vp, vp]
         _lib = L
     return _lib
 
@@ -173,8 +175,9 @@ class Decoder:
 
     def __init__(self, center: Optional[float] = None, width: float = 200.0, step: float = 2.0, depth: int = 4,
                  thr: int = 1, read_mode: int = 1, method: int = 2, device: int = 0, max_batch_blocks: int = 128,
-                 compat_cache: bool = False, flags: int = 0):
+                 compat_cache: bool = False, flags: int = 0, wsjtx_bp: bool = False):
         L = lib()
+        flags |= FLAG_WSJTX_BP if wsjtx_bp else 0
         cfg = _make_config(center, width, step, depth, thr, read_mode, method, device, max_batch_blocks, compat_cache, flags)
         self.cfg = cfg
         self._h = C.c_void_p()
@@ -309,6 +312,15 @@ class Decoder:
 
     def ldpc_decode_device(self, d_llr: int, ncw: int, d_out: int, stream: int = 0):
         _check(lib().msk144_ldpc_decode_device(self._h, d_llr, ncw, d_out, C.c_void_p(stream)))
+
+    def set_ap_mask(self, apmask128: Optional[np.ndarray]):
+        """wsjtx_bp decoders only: bits whose entry is non-zero keep zn = llr (bpdecode128_90's apmask); None clears."""
+        if apmask128 is None:
+            _check(lib().msk144_set_ap_mask(self._h, None))
+        else:
+            a = np.ascontiguousarray(apmask128, np.uint8)
+            assert a.size == 128
+            _check(lib().msk144_set_ap_mask(self._h, a.ctypes.data))
 
     def measure_fp32_peak(self) -> float:
         """Sustained FP32 FMA rate of this decoder's GPU in TFLOP/s (dependency-free FFMA stream, CUDA events)."""

@@ -40,6 +40,7 @@ static void show_help(const char* prog) {
     std::cout << "                   --devices=0,1,...           With --channels=N: split the channels over these GPUs (one host thread and stream set each)." << std::endl;
     std::cout << "                   --batch-blocks=128          Blocks per GPU launch group when input arrives faster than real time." << std::endl;
     std::cout << "                   --per-payload-text          Decode every payload's own text (the reference reuses the first decode of a block)." << std::endl;
+    std::cout << "                   --wsjtx-bp                  LDPC with WSJT-X bpdecode128_90 control flow (11 checks, early stop) instead of the reference kernel's." << std::endl;
     std::cout << "                   --channels=1                stdin carries N channels, one sample of each per time step; lines end with channel=<c>." << std::endl;
     std::cout << "                   --wav                       Skip a RIFF/WAVE header at the start of stdin (the reference decodes it as samples)." << std::endl;
     std::cout << "                   --json                      One JSON object per line instead of the '***' line format." << std::endl;
@@ -79,6 +80,7 @@ int main(int argc, char* const argv[]) {
                                            {"unpack77-lib", required_argument, 0, 0},       // 14
                                            {"channels", required_argument, 0, 0},           // 15
                                            {"devices", required_argument, 0, 0},            // 16
+                                           {"wsjtx-bp", no_argument, 0, 0},                 // 17
                                            {0, 0, 0, 0}};
     while (true) {
         int option_index = 0;
@@ -114,6 +116,7 @@ int main(int argc, char* const argv[]) {
                     while (*q == ',' || *q == ' ') q++;
                 }
                 break;
+            case 17: cfg.flags |= MSK144_FLAG_WSJTX_BP; break;
             default: show_help(argv[0]); return 0;
         }
     }

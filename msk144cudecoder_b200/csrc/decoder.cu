@@ -174,6 +174,7 @@ struct msk144_decoder {
     // streaming state (msk144_push / msk144_poll)
     std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
     int share_twins = std::getenv("MSK144_NO_TWINS") ? 0 : 1;  // A/B knob; results are identical either way
+    unsigned apmask[4] = {0u, 0u, 0u, 0u};  // MSK144_FLAG_WSJTX_BP: a-priori bits (msk144_set_ap_mask)
     // multi-channel streaming state (msk144_push_interleaved): raw interleaved bytes, one SNR recurrence per channel
     int il_nchan = 0;
     std::vector<uint8_t> il_pending;
@@ -369,8 +370,12 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
     lp.result_count = sl.d_counters + 1;
     lp.result_cap = static_cast<int>(std::min<size_t>(result_cap, 0x7fffffffull));
     lp.flat_out = nullptr;
+    std::memcpy(lp.apmask, apmask, sizeof(lp.apmask));
     fill_ldpc_tables(&lp);
-    ldpc_kernel<<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
+    if (cfg.flags & MSK144_FLAG_WSJTX_BP)
+        ldpc_kernel<true><<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
+    else
+        ldpc_kernel<false><<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[3], st));
     CK(cudaEventRecord(sl.done, st));
@@ -972,8 +977,11 @@ int msk144_ldpc_decode_device(msk144_decoder* dec, const float* d_llr, size_t nc
         // caller-supplied LLRs: iteration counts differ from codeword to codeword, so the streaming form (each half
         // of a warp refills on its own) is used; MSK144_LDPC_NO_REFILL=1 selects the pair form for A/B runs
         static const bool no_refill = std::getenv("MSK144_LDPC_NO_REFILL") != nullptr;
-        if (no_refill)
-            ldpc_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
+        if (dec->cfg.flags & MSK144_FLAG_WSJTX_BP) {
+            std::memcpy(lp.apmask, dec->apmask, sizeof(lp.apmask));
+            ldpc_kernel<true><<<grid, LDPC_WARPS * 32, 0, st>>>(lp);  // the pair form carries the WSJT-X control flow
+        } else if (no_refill)
+            ldpc_kernel<false><<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
         else
             ldpc_stream_kernel<<<grid, LDPC_WARPS * 32, 0, st>>>(lp);
         CK(cudaGetLastError());
@@ -1024,6 +1032,16 @@ int msk144_ldpc_decode_host(msk144_decoder* dec, const float* llr, size_t ncw, u
             nhard[i] = (nh == 0xff) ? -1 : nh;
         }
     }
+    return MSK144_OK;
+}
+
+int msk144_set_ap_mask(msk144_decoder* dec, const uint8_t* apmask128) {
+    if (!dec) return fail(MSK144_EINVAL, "null argument");
+    if (!(dec->cfg.flags & MSK144_FLAG_WSJTX_BP)) return fail(MSK144_EINVAL, "a-priori masks belong to MSK144_FLAG_WSJTX_BP");
+    for (int i = 0; i < 4; i++) dec->apmask[i] = 0u;
+    if (apmask128)
+        for (int b = 0; b < 128; b++)
+            if (apmask128[b]) dec->apmask[b >> 5] |= 1u << (b & 31);
     return MSK144_OK;
 }
 

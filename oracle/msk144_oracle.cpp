@@ -507,6 +507,81 @@ int ldpc_decode(const float* llr, uint8_t* msg77, int* iters_out, int* nhard_out
     return 0;
 }
 
+// the same sum-product decoder with the control flow of WSJT-X's
+// bpdecode128_90 as used by its MSK144 decoder, where the reference kernel deviates from it:
+//   * iter = 0 .. maxiterations (10): 11 parity checks and 10 message updates (the reference: 10 and 9);
+//   * the first hard decision that satisfies all parity checks AND the CRC ends the decode; the caller accepts it only
+//     if nharderror < 18 (the reference keeps iterating when nhard >= 18); nharderror counts the bits with
+//     (2 cw - 1) * llr < 0, so an LLR of exactly zero never counts (the reference counts it against a 1 bit);
+//   * early stop: ncnt counts consecutive checks at which the number of unsatisfied parity checks did not decrease;
+//     the decode is abandoned when ncnt >= 3 and iter >= 5 and ncheck > 10;
+//   * apmask: bits marked a-priori keep zn = llr (no extrinsic information is added to them).
+// The arithmetic (tanhf, platanh, product order) is the reference's.  bpdecode128_90.f90 itself is not on this box
+// (deps/wsjtx is an empty submodule): this mode is restated from the published algorithm and its parity with WSJT-X is
+// UNPINNED; what the tests pin is kernel == this function, bit for bit.
+int ldpc_decode_wsjtx(const float* llr, const uint8_t* apmask, uint8_t* msg77, int* iters_out, int* nhard_out) {
+    constexpr int MAXIT = 10;
+    float toc[11][38], tov[3][128], zn[128];
+    uint8_t cw[128];
+    for (int k = 0; k < 3; k++)
+        for (int b = 0; b < 128; b++) tov[k][b] = 0.0f;
+    for (int c = 0; c < 38; c++) toc[10][c] = 0.0f;
+    int ncnt = 0, nclast = 0;
+    for (int iter = 0; iter <= MAXIT; iter++) {
+        for (int b = 0; b < 128; b++) {
+            float sum = 0.0f;
+            for (int k = 0; k < 3; k++) sum += tov[k][b];
+            zn[b] = (apmask && apmask[b]) ? llr[b] : llr[b] + sum;
+            cw[b] = (zn[b] > 0.0f) ? 1 : 0;
+        }
+        int ncheck = 0;
+        for (int c = 0; c < 38; c++) {
+            int s = 0;
+            for (int j = 0; j < L.nrw[c]; j++) s += cw[ORC_NM[c][j]];
+            ncheck += s % 2;
+        }
+        if (ncheck == 0) {
+            unsigned char bytes[16];
+            bits_to_bytes(cw, 128, bytes);
+            if (check_crc(bytes)) {
+                int nhard = 0;
+                for (int b = 0; b < 128; b++) nhard += ((cw[b] ? 1.0f : -1.0f) * llr[b] < 0.0f) ? 1 : 0;
+                std::memcpy(msg77, cw, 77);
+                *iters_out = iter;
+                *nhard_out = nhard;
+                return nhard < 18 ? 1 : 0;
+            }
+        }
+        if (iter > 0) {
+            if (ncheck - nclast < 0) ncnt = 0;
+            else ncnt++;
+            if (ncnt >= 3 && iter >= 5 && ncheck > 10) {
+                *iters_out = iter;
+                *nhard_out = -1;
+                return 0;
+            }
+        }
+        nclast = ncheck;
+        if (iter == MAXIT) break;
+        for (int b = 0; b < 128; b++)
+            for (int k = 0; k < 3; k++) toc[L.slot[b][k]][L.chk[b][k]] = zn[b] - tov[k][b];
+        float th[11][38];
+        for (int c = 0; c < 38; c++)
+            for (int j = 0; j < L.nrw[c]; j++) th[j][c] = tanhf(-0.5f * toc[j][c]);
+        for (int b = 0; b < 128; b++)
+            for (int k = 0; k < 3; k++) {
+                const int c = L.chk[b][k], ex = L.slot[b][k];
+                float product = 1.0f;
+                for (int j = 0; j < L.nrw[c]; j++)
+                    if (j != ex) product *= th[j][c];
+                tov[k][b] = 2.0f * platanh(-product);
+            }
+    }
+    *iters_out = MAXIT + 1;
+    *nhard_out = -1;
+    return 0;
+}
+
 // ---------------------------------------------------------------- front end
 // analytic2.cuh:93-233.  The per-slice read-all/sync/write-all structure of the reference makes
 // both in-place passes equal to out-of-place FIRs; we emulate the slices literally anyway.
@@ -708,6 +783,7 @@ void decode_block_impl(const C* x, const orc_config* cfg, orc_item* items, bool 
     const Grid g = make_grid(cfg->center_hz, cfg->width_hz, cfg->step_hz);
     const int depth = clamp_depth(cfg->scan_depth);
     const int thr = cfg->nbadsync_threshold;
+    const bool cfg_wsjtx_bp = cfg->wsjtx_bp != 0;
     parallel_for(g.nf, parallel ? cfg->nthreads : 1, [&](long long fi_) {
         const int fi = (int)fi_;
         std::vector<C> cdat2(N);
@@ -731,7 +807,8 @@ void decode_block_impl(const C* x, const orc_config* cfg, orc_item* items, bool 
                 softbits_from_mixed(cdat2.data(), p, it.pos, it.llr, &it.nbadsync, nullptr);
                 if (it.nbadsync <= thr) {  // index_kernel.cuh:17-75
                     int iters = 0, nhard = 0;
-                    if (ldpc_decode(it.llr, it.message, &iters, &nhard)) {
+                    if (cfg_wsjtx_bp ? ldpc_decode_wsjtx(it.llr, nullptr, it.message, &iters, &nhard)
+                                     : ldpc_decode(it.llr, it.message, &iters, &nhard)) {
                         it.is_message_present = 1;
                         it.ldpc_iters = iters;
                         it.ldpc_nhard = nhard;
@@ -881,6 +958,23 @@ void orc_ldpc_decode_batch(const float* llr, size_t ncw, uint8_t* found, uint8_t
             uint8_t m[80] = {0};
             int it = 0, nh = 0;
             const int f = ldpc_decode(llr + 128 * i, m, &it, &nh);
+            found[i] = (uint8_t)f;
+            if (msg77) std::memcpy(msg77 + 77 * i, m, 77);
+            if (iters) iters[i] = it;
+            if (nhard) nhard[i] = nh;
+        }
+    });
+}
+
+void orc_ldpc_decode_wsjtx_batch(const float* llr, size_t ncw, const uint8_t* apmask128, uint8_t* found, uint8_t* msg77,
+                                 int32_t* iters, int32_t* nhard, int nthreads) {
+    const long long chunk = 1024, nchunks = ((long long)ncw + chunk - 1) / chunk;
+    parallel_for(nchunks, nthreads, [&](long long ci) {
+        const long long hi = std::min<long long>((long long)ncw, (ci + 1) * chunk);
+        for (long long i = ci * chunk; i < hi; i++) {
+            uint8_t m[80] = {0};
+            int it = 0, nh = 0;
+            const int f = ldpc_decode_wsjtx(llr + 128 * i, apmask128, m, &it, &nh);
             found[i] = (uint8_t)f;
             if (msg77) std::memcpy(msg77 + 77 * i, m, 77);
             if (iters) iters[i] = it;

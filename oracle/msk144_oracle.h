@@ -63,6 +63,8 @@ typedef struct orc_config {
     int   scan_mode;        /* 0 = reference summation order (brute force), 1 = linear reformulation */
     int   compat_cache;     /* 1 = reproduce the decode_cache comparator quirk (main.cu:430-447) */
     int   nthreads;         /* OpenMP threads, 0 = default */
+    int   wsjtx_bp;         /* 1 = LDPC with WSJT-X bpdecode128_90 control flow (11 checks, early stop) instead of the
+                               reference kernel's (10 checks, none) */
 } orc_config;
 
 /* ---- grid / tables (msk_context.cuh:95-113,137-248) ---- */
@@ -96,6 +98,10 @@ int      orc_ldpc_decode(const float* llr128, uint8_t* msg77, int* iters, int* n
 void     orc_ldpc_decode_batch(const float* llr, size_t ncw, uint8_t* found, uint8_t* msg77,
                                int32_t* iters, int32_t* nhard, int nthreads);
 uint32_t orc_crc13(const uint8_t* bits77);
+/* the same decoder with WSJT-X bpdecode128_90 control flow (11 checks, early stop, a-priori mask; see the .cpp);
+ * apmask128: 128 bytes of 0/1 common to all codewords, or NULL */
+void     orc_ldpc_decode_wsjtx_batch(const float* llr, size_t ncw, const uint8_t* apmask128, uint8_t* found,
+                                     uint8_t* msg77, int32_t* iters, int32_t* nhard, int nthreads);
 void     orc_ldpc_encode(const uint8_t* msg77, uint8_t* cw128);
 void     orc_ldpc_parity_matrix(uint8_t* h /*38*128*/);
 

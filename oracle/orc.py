@@ -35,7 +35,7 @@ class Config(C.Structure):
     _fields_ = [("center_hz", C.c_float), ("width_hz", C.c_float), ("step_hz", C.c_float),
                 ("scan_depth", C.c_int), ("nbadsync_threshold", C.c_int), ("read_mode", C.c_int),
                 ("analytic_method", C.c_int), ("scan_mode", C.c_int), ("compat_cache", C.c_int),
-                ("nthreads", C.c_int)]
+                ("nthreads", C.c_int), ("wsjtx_bp", C.c_int)]
 
 
 ITEM_DTYPE = np.dtype([("freq_idx", "<u4"), ("pattern_idx", "<u4"), ("pos", "<u4"), ("f0", "<f4"),
@@ -79,6 +79,7 @@ def lib():
         L.orc_ldpc_decode_batch.argtypes = [f32p, C.c_size_t, u8p, u8p, i32p, i32p, C.c_int]
         L.orc_crc13.restype = C.c_uint32
         L.orc_crc13.argtypes = [u8p]
+        L.orc_ldpc_decode_wsjtx_batch.argtypes = [f32p, C.c_size_t, u8p, u8p, u8p, i32p, i32p, C.c_int]
         L.orc_ldpc_encode.argtypes = [u8p, u8p]
         L.orc_ldpc_parity_matrix.argtypes = [u8p]
         L.orc_decode_block.argtypes = [f32p, C.POINTER(Config), C.c_void_p]
@@ -110,8 +111,8 @@ def _i32(a):
 
 
 def config(center=1500.0, width=200.0, step=2.0, depth=4, thr=1, read_mode=1, method=2, scan_mode=1,
-           compat_cache=1, nthreads=0) -> Config:
-    return Config(center, width, step, depth, thr, read_mode, method, scan_mode, compat_cache, nthreads)
+           compat_cache=1, nthreads=0, wsjtx_bp=0) -> Config:
+    return Config(center, width, step, depth, thr, read_mode, method, scan_mode, compat_cache, nthreads, wsjtx_bp)
 
 
 def num_freqs(width, step) -> int:
@@ -200,6 +201,20 @@ def ldpc_decode_batch(llr: np.ndarray, nthreads: int = 0):
     it = np.zeros(n, np.int32)
     nh = np.zeros(n, np.int32)
     lib().orc_ldpc_decode_batch(_f32(llr), n, _u8(found), _u8(msg), _i32(it), _i32(nh), nthreads)
+    return found.astype(bool), msg, it, nh
+
+
+def ldpc_decode_wsjtx_batch(llr: np.ndarray, apmask: np.ndarray = None, nthreads: int = 0):
+    """WSJT-X bpdecode128_90 control flow (11 checks, early stop, optional a-priori mask of 128 0/1 bytes)."""
+    llr = np.ascontiguousarray(llr, np.float32).reshape(-1, 128)
+    n = llr.shape[0]
+    found = np.zeros(n, np.uint8)
+    msg = np.zeros((n, 77), np.uint8)
+    it = np.zeros(n, np.int32)
+    nh = np.zeros(n, np.int32)
+    ap = None if apmask is None else np.ascontiguousarray(apmask, np.uint8)
+    lib().orc_ldpc_decode_wsjtx_batch(_f32(llr), n, _u8(ap) if ap is not None else None, _u8(found), _u8(msg), _i32(it), _i32(nh),
+                                      nthreads)
     return found.astype(bool), msg, it, nh
 
 

@@ -17,6 +17,13 @@ pytestmark = pytest.mark.gpu
 
 LLR_TOL = 1e-4   # max |llr_gpu - llr_oracle| / rms(llr_oracle)
 XB_TOL = 1e-5    # relative
+# Bounds on the discrete differences between the GPU and the CPU oracle (glibc vs libdevice sincosf / hypotf / tanhf in
+# the last ulp can move a near-tie).  Each test prints what it observed; the bounds are the observed values plus margin
+# (profiles/r02_notes.md records the observations).
+SET_AGREE_MIN = 0.98     # fraction of (frequency, pattern) groups with the same 8 positions
+SAME_SLOT_MIN = 0.99     # fraction of asymmetric-pattern candidates in the same slot
+NBAD_DIFFER_MAX = 1      # candidates whose nbadsync differs (a sync soft bit within rounding of zero)
+FLAG_MISMATCH_MAX = 2    # LDPC verdicts / iteration counts / hard-error counts out of ~17,000 codewords
 
 
 @pytest.fixture(scope="module")
@@ -69,13 +76,17 @@ def test_scan_softbits_match_oracle(gpu, orc, synth, depth, thr):
         cands, llr, llr_item = d.scan(blk[None, :])
     cands = cands[0]
     assert len(cands) == len(ref)
-    assert candidate_set_agreement(cands["pos"], ref["pos"], depth) > 0.98
+    agree = candidate_set_agreement(cands["pos"], ref["pos"], depth)
     same = cands["pos"] == ref["pos"]
     pat = ref["pattern_idx"]
-    assert same[(pat != 5) & (pat != 6)].mean() > 0.99
+    same_slot = same[(pat != 5) & (pat != 6)].mean()
+    nbad_differ = int((cands["nbadsync"][same] != ref["nbadsync"][same]).sum())
+    print(f"depth {depth}: candidate sets agree in {agree:.4f} of the (frequency, pattern) groups, same slot in {same_slot:.4f} of the "
+          f"asymmetric-pattern candidates, nbadsync differs in {nbad_differ} of {int(same.sum())}")
+    assert agree >= SET_AGREE_MIN and same_slot >= SAME_SLOT_MIN
     assert np.max(np.abs(cands["xb"][same] - ref["xb"][same]) / ref["xb"][same]) < XB_TOL
     # sync gate: identical where the position is identical (a sync soft bit within rounding of 0 could flip)
-    assert (cands["nbadsync"][same] == ref["nbadsync"][same]).mean() > 0.999
+    assert nbad_differ <= NBAD_DIFFER_MAX
     # LLRs of gated candidates
     gated = np.where(same & (cands["llr_slot"] >= 0) & (ref["nbadsync"] <= thr))[0]
     assert len(gated) > 20
@@ -85,6 +96,7 @@ def test_scan_softbits_match_oracle(gpu, orc, synth, depth, thr):
         g = llr[row_of[int(i)]]
         r = ref["llr"][i]
         worst = max(worst, float(np.max(np.abs(g - r)) / np.sqrt(np.mean(r ** 2))))
+    print(f"depth {depth}: worst |dLLR| / rms over {len(gated)} gated candidates {worst:.2e} (bound {LLR_TOL:.0e})")
     assert worst < LLR_TOL, worst
     # every candidate that passed the gate on the GPU has exactly one queue row
     assert sorted(row_of) == sorted(np.where(cands["llr_slot"] >= 0)[0].tolist())
@@ -111,9 +123,12 @@ def test_ldpc_matches_oracle(gpu, orc, synth):
         fg, mg, ig, ng = d.ldpc_decode(llr_all)
     flag_mismatch = int((fo != fg).sum())
     both = fo & fg
-    assert flag_mismatch <= 2, flag_mismatch                # tanhf last-ulp differences only
+    it_mismatch, nh_mismatch = int((ig[both] != io[both]).sum()), int((ng[both] != no[both]).sum())
+    print(f"GPU vs CPU oracle over {len(llr_all)} codewords: {flag_mismatch} decode flags, {it_mismatch} iteration counts, "
+          f"{nh_mismatch} hard-error counts differ (glibc vs libdevice tanhf, last ulp)")
+    assert flag_mismatch <= FLAG_MISMATCH_MAX, flag_mismatch
     assert (mo[both] == mg[both]).all()
-    assert (ig[both] != io[both]).sum() <= 2 and (ng[both] != no[both]).sum() <= 2
+    assert it_mismatch <= FLAG_MISMATCH_MAX and nh_mismatch <= FLAG_MISMATCH_MAX
     assert (ig[~fg] == 10).all() and (ng[~fg] == -1).all()
     # whatever decodes is a real codeword of the transmitted payload
     n = len(llr)
@@ -329,3 +344,43 @@ def test_multichannel_streaming_equals_single_channel_streams(gpu, synth):
     import re
     cli = sorted((int(re.search(r"channel=(\d+); $", l).group(1)), re.search(r"msg='(.*)';", l).group(1)) for l in out[:-1])
     assert cli == sorted((l["channel"], l["text"]) for l in want)
+
+
+@pytest.mark.gpu
+def test_wsjtx_bp_kernel_matches_oracle(gpu, orc, synth):
+    """MSK144_FLAG_WSJTX_BP: ldpc_kernel<true> against the oracle's restatement of bpdecode128_90's control flow over the
+    cfg4 sweep, pure noise, degenerate inputs, and with an a-priori mask.  (bpdecode128_90.f90 itself is not on this box.)"""
+    llrs = [synth.cfg4_llrs(2500, float(e), seed=160 + e)[0] for e in range(8)]
+    rng = np.random.default_rng(11)
+    llrs += [(rng.standard_normal((6000, 128)) * 5.5).astype(np.float32), np.zeros((3, 128), np.float32)]
+    z = llrs[3][:300].copy()
+    z[:, ::5] = 0.0                       # exact zeros: nharderror must not count them
+    llr = np.concatenate(llrs + [z])
+    for ap in (None, (np.arange(128) < 28).astype(np.uint8)):
+        fo, mo, io, no = orc.ldpc_decode_wsjtx_batch(llr, ap, 8)
+        with gpu.Decoder(width=20, depth=1, wsjtx_bp=True) as d:
+            d.set_ap_mask(ap)
+            fg, mg, ig, ng = d.ldpc_decode(llr)
+        mism = int((fo != fg).sum())
+        both = fo & fg
+        it_mism, nh_mism = int((ig != io).sum()), int((ng[both] != no[both]).sum())
+        print(f"WSJT-X BP, apmask {'on' if ap is not None else 'off'}: {len(llr)} codewords, {int(fg.sum())} decoded, {mism} verdicts, "
+              f"{it_mism} iteration counts (incl. early stops), {nh_mism} hard-error counts differ from the CPU oracle")
+        assert mism <= FLAG_MISMATCH_MAX and it_mism <= 2 * FLAG_MISMATCH_MAX and nh_mism <= FLAG_MISMATCH_MAX
+        assert (mo[both] == mg[both]).all()
+        assert ((ig[~fg] >= 5) | (ng[~fg] >= 18)).all() and (ig <= 11).all()
+    # the flag changes nothing for a decoder that does not set it, and a mask needs the flag
+    with gpu.Decoder(width=20, depth=1) as d:
+        with pytest.raises(gpu.Msk144Error):
+            d.set_ap_mask(np.zeros(128, np.uint8))
+
+
+@pytest.mark.gpu
+def test_wsjtx_bp_stream_matches_oracle(gpu, orc, synth):
+    """The whole pipeline with the flag: decode lines equal the oracle's with wsjtx_bp = 1."""
+    x, pings = synth.cfg1_demo(seconds=6.0, seed=5)
+    kw = dict(width=100, step=2, depth=3, thr=2)
+    ref, nb = orc.decode_stream(x, orc.config(compat_cache=1, wsjtx_bp=1, nthreads=8, **kw))
+    with gpu.Decoder(compat_cache=True, wsjtx_bp=True, **kw) as d:
+        lines, _ = d.decode_host(x)
+    assert len(ref) > 0 and lines_key(lines) == lines_key(ref)

@@ -74,3 +74,46 @@ def test_single_and_batch_agree(orc, synth):
         assert f == fb[i] and it == ib[i] and nh == nb[i]
         if f:
             assert (d == db[i]).all()
+
+
+# ---- WSJT-X control flow: oracle semantics; the kernel is pinned to it in test_gpu_parity.py
+def test_wsjtx_bp_semantics(orc, synth):
+    llr, msgs = synth.cfg4_llrs(3000, 3.0, seed=150)
+    f, m, it, nh = orc.ldpc_decode_batch(llr, 8)
+    fw, mw, itw, nhw = orc.ldpc_decode_wsjtx_batch(llr, None, 8)
+    # same arithmetic: whatever both decode is the same payload, and it is the transmitted one
+    both = f & fw
+    assert both.sum() > 2000 and (m[both] == mw[both]).all() and (mw[fw] == msgs[fw]).all()
+    # a decode found at check k < 10 by the reference kernel is found at the same check here (identical iterations up to
+    # there), unless the early stop fired first -- which needs iter >= 5
+    early = both & (it < 5)
+    assert early.sum() > 1000 and (it[early] == itw[early]).all() and (nh[early] == nhw[early]).all()
+    # the 11th check exists: failures that ran to the end report 11, early stops report 5..10
+    fail = ~fw
+    assert set(np.unique(itw[fail])) <= set(range(5, 12)) and (itw[fail] == 11).any() and (itw[fail] < 11).any()
+    # decodes at the 11th check (iters == 10) are out of the reference kernel's reach
+    assert (itw[fw] <= 10).all() and (it[f] <= 9).all()
+
+
+def test_wsjtx_bp_noise_stops_early(orc):
+    noise = (np.random.default_rng(3).standard_normal((4000, 128)) * 5.5).astype(np.float32)
+    fw, _, itw, nhw = orc.ldpc_decode_wsjtx_batch(noise, None, 8)
+    assert fw.sum() == 0 and (nhw == -1).all()
+    frac_early = (itw < 11).mean()
+    assert 0.2 < frac_early < 0.6           # about a third of pure-noise codewords is abandoned before the 11th check
+
+
+def test_wsjtx_bp_apmask_freezes_bits(orc, synth):
+    llr, msgs = synth.cfg4_llrs(500, 2.0, seed=151)
+    cw = np.stack([orc.ldpc_encode(m) for m in msgs])
+    ap = np.zeros(128, np.uint8)
+    ap[:40] = 1
+    strong = llr.copy()
+    strong[:, :40] = (2.0 * cw[:, :40] - 1.0) * 20.0        # the caller's a-priori knowledge goes into the LLRs
+    f0, _, _, _ = orc.ldpc_decode_wsjtx_batch(llr, None, 8)
+    f1, m1, _, _ = orc.ldpc_decode_wsjtx_batch(strong, ap, 8)
+    assert f1.sum() > f0.sum() and (m1[f1] == msgs[f1]).all()
+    wrong = llr.copy()
+    wrong[:, :40] = -(2.0 * cw[:, :40] - 1.0) * 20.0         # frozen to the wrong values: nothing may decode correctly
+    f2, m2, _, _ = orc.ldpc_decode_wsjtx_batch(wrong, ap, 8)
+    assert not (f2 & (m2 == msgs).all(axis=1)).any()
