@@ -325,7 +325,8 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
         fp.hfilt = d_hfilt;
         fp.out = sl.d_blocks;
         fp.powers = sl.d_powers;
-        fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, st>>>(fp);
+        fp.nblocks = nb;
+        fft_frontend_kernel<<<std::min(nb, sm_count), FFT_THREADS, FFT_SMEM, st>>>(fp);
     } else {
         FrontParams fp;
         fp.raw = d_in;
@@ -868,7 +869,8 @@ int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsampl
             fp.hfilt = dec->d_hfilt;
             fp.out = dec->slot[0].d_blocks;
             fp.powers = dec->slot[0].d_powers;
-            fft_frontend_kernel<<<nb, FFT_THREADS, FFT_SMEM, dec->stream>>>(fp);
+            fp.nblocks = nb;
+            fft_frontend_kernel<<<std::min(nb, dec->sm_count), FFT_THREADS, FFT_SMEM, dec->stream>>>(fp);
         } else {
             FrontParams fp;
             fp.raw = dec->d_raw;

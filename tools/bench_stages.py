@@ -56,6 +56,28 @@ def main():
                               "decoded_frac": found / n, "mean_iters": iters,
                               "hbm_gbs": n * 528 / ms / 1e6}), flush=True)
         dec.close()
+    if "frontend" in which:
+        # front-end kernels alone (CUDA events around the kernel inside the library): method 2 (frontend_kernel) and
+        # method 1 (fft_frontend_kernel), launch groups of 128 blocks (the stream pipeline's) and of 4096 (cfg5's scale)
+        x1, _ = synth.cfg2_deep_audio(seconds=60.0, seed=144)
+        for nchan, batch in ((1, 128), (16, 4096)):
+            xs = np.ascontiguousarray(np.tile(x1, nchan))
+            xd = torch.from_numpy(xs).to(dev)
+            for method in (2, 1):
+                dec = m.Decoder(compat_cache=True, max_batch_blocks=batch, width=20.0, step=2.0, depth=1, thr=1, method=method)
+                s = torch.cuda.Stream()
+                for _ in range(2):
+                    nb = dec.run_device(xd.data_ptr(), len(x1), nchan, s.cuda_stream)
+                torch.cuda.synchronize()
+                dec.stage_times()
+                for _ in range(5):
+                    dec.run_device(xd.data_ptr(), len(x1), nchan, s.cuda_stream)
+                st = dec.stage_times()
+                us = st["frontend_ms"] * 1e3 / st["blocks"]
+                print(json.dumps({"bench": "frontend", "lib": os.path.basename(m.LIB_PATH), "method": method, "blocks_per_launch": min(batch, nb),
+                                  "us_per_block": us, "algorithmic_gbs": (5184 * 2 + 5184 * 8 + 32) / us / 1e3,
+                                  "launch_ms": st["frontend_ms"] / st["groups"]}), flush=True)
+                dec.close()
     if "scan" in which:
         x, _ = synth.cfg2_deep_audio(seconds=60.0, seed=144)
         xd = torch.from_numpy(x).to(dev)

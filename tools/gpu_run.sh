@@ -28,6 +28,7 @@ for step in "$@"; do
       $CMD > gpurun_out/ncu_plain2.log 2>&1 &&
       ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 0 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
       echo "ncu_full rc=$?"; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/*.ncu-rep ;;
+    warpops) ./scratch/warpops > gpurun_out/warpops.txt 2>&1; cat gpurun_out/warpops.txt ;;
     scanprof) for so in scratch/variants_prof/*.so; do echo "== $so"; MSK144_B200_LIB=$PWD/$so timeout 300 python tools/scan_prof.py 2>&1 | tail -20; done > gpurun_out/scanprof.log 2>&1; cat gpurun_out/scanprof.log ;;
     golden_multi) timeout 1500 python -m pytest tests/test_golden.py tests/test_gpu_multi.py -m gpu -q --timeout=900 -s > gpurun_out/pytest_gm.log 2>&1; echo "golden_multi rc=$?"; grep -E "passed|failed|_60s:|Error" gpurun_out/pytest_gm.log | tail -20 ;;
     *) echo "unknown step $step" ;;
