@@ -281,6 +281,45 @@ int msk144_pool_push_interleaved(msk144_pool* pool, const void* bytes, size_t nb
 int msk144_pool_poll(msk144_pool* pool, msk144_line* lines, size_t cap, size_t* nlines);
 int msk144_pool_reset_stream(msk144_pool* pool);
 
+/* ---- channeliser in front of the decoder (ingest side) ---------------------------------------
+ * The reference reads ONE channel that something else has already brought to 12 ksps; its README documents the chain
+ *   rtl_sdr -s 1920000 ... | csdr convert_u8_f | fir_decimate_cc 8 | 5 | 4 | gain_ff 100 | convert_f_s8   (README.md:75-78)
+ * This does that step on the GPU for any number of channels of one wideband capture at once: a uniform polyphase
+ * filter bank with decimation M = input rate / 12000.  Channel c is centred bins[c] x 12 kHz from the centre of the
+ * capture (|bin| < M, negative = below) and leaves as s8 I,Q pairs at 12 ksps, the input format of --read-mode=2:
+ *   out = saturate_s8(round_to_nearest_even(127 x gain x y)),  y = low-passed sample relative to full scale
+ *   (full scale: u8 (v - 127.5) / 127.5, s8 v / 128, s16 v / 32768; saturation at +-127).
+ * Prototype low-pass: 8 M taps, Kaiser beta 7.857, -6 dB at 6 kHz, unit DC gain (msk144_channelizer_prototype returns it).
+ * csdr itself is not on this box: the filter is this library's own design, not csdr's.  No CPU fallback. */
+enum { MSK144_IQ_U8 = 1, MSK144_IQ_S8 = 2, MSK144_IQ_S16 = 3 };
+typedef struct msk144_channelizer_config {
+    int32_t input_format; /* MSK144_IQ_*: interleaved I,Q */
+    int32_t decimation;   /* M, 2..256: input rate = M x 12000 samples/s (160 for rtl_sdr -s 1920000) */
+    float gain;           /* csdr gain_ff; 100 in the README's recipe */
+    int32_t device;       /* CUDA device ordinal */
+    int32_t reserved[4];
+} msk144_channelizer_config;
+typedef struct msk144_channelizer msk144_channelizer;
+int msk144_channelizer_create(const msk144_channelizer_config* cfg, const int32_t* bins, int32_t nbins, msk144_channelizer** out);
+void msk144_channelizer_destroy(msk144_channelizer* chz);
+int msk144_channelizer_prototype(const msk144_channelizer* chz, float* taps, size_t cap, size_t* ntaps);
+int64_t msk144_channelizer_launches(const msk144_channelizer* chz); /* kernels launched since creation */
+/* Resident input -> resident output, asynchronous on `stream` (cudaStream_t, NULL = the channeliser's own).  d_in points
+ * at the first sample of frame 0 (a frame = M input samples = one output sample per channel); `history_frames` (0..7)
+ * whole frames BEFORE d_in are valid and are used as filter history, anything earlier counts as zero.  Output sample
+ * (channel c, frame f) is the byte pair at d_out + 2 (c x out_chan_stride + f x out_frame_stride): strides (nframes
+ * rounded up to 8, 1) give the channel-major layout of msk144_decode_device, (1, nchan) the time-major layout of
+ * msk144_push_interleaved. */
+int msk144_channelize_device(msk144_channelizer* chz, const void* d_in, size_t nframes, int32_t history_frames, void* d_out,
+                             size_t out_chan_stride, size_t out_frame_stride, void* stream);
+/* One capture in host memory -> out[nchan][*nframes][2], *nframes = whole frames in nbytes; zero history. */
+int msk144_channelize_host(msk144_channelizer* chz, const void* in, size_t nbytes, int8_t* out, size_t out_cap_frames, size_t* nframes);
+/* Streaming: push any number of bytes; whole frames come back time-major, out[*nframes][nchan][2] (feed them to
+ * msk144_push_interleaved, or msk144_push for one channel); the filter history and a partial frame are kept inside.
+ * MSK144_EOVERFLOW (nothing consumed, *nframes = frames needed) if out_cap_frames is too small. */
+int msk144_channelizer_push(msk144_channelizer* chz, const void* bytes, size_t nbytes, int8_t* out, size_t out_cap_frames, size_t* nframes);
+int msk144_channelizer_reset(msk144_channelizer* chz);
+
 /* ---- measurement helpers -------------------------------------------------------------------------------------- */
 /* Sustained FP32 FMA rate of the decoder's device: a dependency-free FFMA stream (8 independent chains per thread,
  * every SM sub-partition saturated), timed with CUDA events; *tflops = 2 * FMAs / time.  This is the measured

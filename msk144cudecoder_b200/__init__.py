@@ -37,7 +37,10 @@ EXPORTED_SYMBOLS = [
     "msk144_pool_last_error", "msk144_pool_create", "msk144_pool_destroy", "msk144_pool_size", "msk144_pool_member",
     "msk144_pool_decode_host", "msk144_pool_push_interleaved", "msk144_pool_poll", "msk144_pool_reset_stream",
     "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math", "msk144_set_ap_mask",
+    "msk144_channelizer_create", "msk144_channelizer_destroy", "msk144_channelizer_prototype", "msk144_channelizer_launches",
+    "msk144_channelize_device", "msk144_channelize_host", "msk144_channelizer_push", "msk144_channelizer_reset",
 ]
+IQ_U8, IQ_S8, IQ_S16 = 1, 2, 3
 
 
 class Msk144Error(RuntimeError):
@@ -49,6 +52,11 @@ class Config(C.Structure):
                 ("scan_depth", C.c_int32), ("read_mode", C.c_int32), ("analytic_method", C.c_int32),
                 ("nbadsync_threshold", C.c_int32), ("device", C.c_int32), ("max_batch_blocks", C.c_int32),
                 ("flags", C.c_int32), ("reserved", C.c_int32 * 6)]
+
+
+class ChannelizerConfig(C.Structure):
+    _fields_ = [("input_format", C.c_int32), ("decimation", C.c_int32), ("gain", C.c_float), ("device", C.c_int32),
+                ("reserved", C.c_int32 * 4)]
 
 
 class Line(C.Structure):
@@ -150,6 +158,16 @@ def lib():
         L.msk144_measure_fp32_peak.argtypes = [vp, C.POINTER(C.c_double)]
         L.msk144_build_info.restype = C.c_char_p
         L.msk144_set_ap_mask.argtypes = [vp, vp]
+        L.msk144_channelizer_create.argtypes = [C.POINTER(ChannelizerConfig), C.POINTER(C.c_int32), C.c_int32, C.POINTER(vp)]
+        L.msk144_channelizer_destroy.argtypes = [vp]
+        L.msk144_channelizer_destroy.restype = None
+        L.msk144_channelizer_prototype.argtypes = [vp, vp, sz, C.POINTER(sz)]
+        L.msk144_channelizer_launches.argtypes = [vp]
+        L.msk144_channelizer_launches.restype = C.c_int64
+        L.msk144_channelize_device.argtypes = [vp, vp, sz, C.c_int32, vp, sz, sz, vp]
+        L.msk144_channelize_host.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
+        L.msk144_channelizer_push.argtypes = [vp, vp, sz, vp, sz, C.POINTER(sz)]
+        L.msk144_channelizer_reset.argtypes = [vp]
         _lib = L
     return _lib
 
@@ -394,6 +412,72 @@ class Pool:
     def close(self):
         if getattr(self, "_h", None) is not None and self._h:
             lib().msk144_pool_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+
+class Channelizer:
+    """Wideband I/Q capture -> channels of 12 ksps s8 I/Q (msk144_channelizer_*): the GPU version of the README's
+    `csdr fir_decimate_cc 8 | 5 | 4 | gain_ff 100 | convert_f_s8` chain (README.md:75-78), for many channels at once.
+    `bins[c]` x 12 kHz is the offset of channel c from the centre of the capture."""
+
+    def __init__(self, decimation: int, bins: List[int], input_format: int = IQ_U8, gain: float = 100.0, device: int = 0):
+        cfg = ChannelizerConfig(input_format=input_format, decimation=decimation, gain=gain, device=device)
+        arr = (C.c_int32 * len(bins))(*bins)
+        self._h = C.c_void_p()
+        _check(lib().msk144_channelizer_create(C.byref(cfg), arr, len(bins), C.byref(self._h)))
+        self.bins, self.decimation, self.input_format = list(bins), decimation, input_format
+        self.sample_bytes = 4 if input_format == IQ_S16 else 2
+
+    def prototype(self) -> np.ndarray:
+        n = C.c_size_t(0)
+        _check(lib().msk144_channelizer_prototype(self._h, None, 0, C.byref(n)))
+        taps = np.zeros(n.value, np.float32)
+        _check(lib().msk144_channelizer_prototype(self._h, taps.ctypes.data, n.value, C.byref(n)))
+        return taps
+
+    def launches(self) -> int:
+        return int(lib().msk144_channelizer_launches(self._h))
+
+    def channelize_host(self, capture: np.ndarray) -> np.ndarray:
+        """capture: interleaved I,Q (u8 / s8 / s16 as configured) -> int8 [nchan][nframes][2]"""
+        capture = np.ascontiguousarray(capture)
+        nf = capture.nbytes // (self.decimation * self.sample_bytes)
+        out = np.zeros((len(self.bins), nf, 2), np.int8)
+        n = C.c_size_t(0)
+        _check(lib().msk144_channelize_host(self._h, capture.ctypes.data, capture.nbytes, out.ctypes.data, nf, C.byref(n)))
+        assert n.value == nf
+        return out
+
+    def channelize_device(self, d_in: int, nframes: int, d_out: int, chan_stride: int, frame_stride: int = 1,
+                          history_frames: int = 0, stream: int = 0):
+        _check(lib().msk144_channelize_device(self._h, d_in, nframes, history_frames, d_out, chan_stride, frame_stride, stream))
+
+    def push(self, data: bytes) -> np.ndarray:
+        """-> int8 [nframes][nchan][2], the time-major layout Decoder.push(..., nchan) takes"""
+        cap = (len(data) // (self.decimation * self.sample_bytes)) + 1
+        out = np.zeros((cap, len(self.bins), 2), np.int8)
+        n = C.c_size_t(0)
+        _check(lib().msk144_channelizer_push(self._h, data, len(data), out.ctypes.data, cap, C.byref(n)))
+        return out[:n.value]
+
+    def reset(self):
+        _check(lib().msk144_channelizer_reset(self._h))
+
+    def close(self):
+        if getattr(self, "_h", None) is not None and self._h:
+            lib().msk144_channelizer_destroy(self._h)
             self._h = C.c_void_p()
 
     def __enter__(self):

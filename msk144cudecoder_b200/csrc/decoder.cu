@@ -145,6 +145,7 @@ struct msk144_decoder {
     struct Slot {
         float2* d_blocks = nullptr;
         float* d_powers = nullptr;
+        float* d_fac = nullptr;  // 1 / rms per block (rms_kernel)
         CandRec* d_cands = nullptr;
         QueueRec* d_queue = nullptr;
         ResultRec* d_results = nullptr;
@@ -190,6 +191,7 @@ struct msk144_decoder {
     int ensure_capacity(int nblocks);
     int ensure_raw(size_t bytes);
     int ensure_host_results(size_t n);
+    int launch_frontend(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
     int launch_group(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb, cudaStream_t st);
     int fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, int64_t gblock0, std::vector<float>* powers);
     int next_events(EvQuad** q);
@@ -218,7 +220,7 @@ struct msk144_decoder {
 void msk144_decoder::release() {
     cudaSetDevice(cfg.device);
     for (Slot& sl : slot) {
-        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
+        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_fac), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
         cudaFree(sl.d_counters);
         if (sl.h_counters) cudaFreeHost(sl.h_counters);
         if (sl.h_powers) cudaFreeHost(sl.h_powers);
@@ -248,11 +250,12 @@ int msk144_decoder::ensure_capacity(int nblocks) {
     result_cap = nb * items;
     if (queue_cap > 0x7fffffffull) return fail(MSK144_EINVAL, "batch too large");
     for (Slot& sl : slot) {
-        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
-        sl.d_blocks = nullptr, sl.d_powers = nullptr, sl.d_cands = nullptr, sl.d_queue = nullptr, sl.d_results = nullptr;
+        cudaFree(sl.d_blocks), cudaFree(sl.d_powers), cudaFree(sl.d_fac), cudaFree(sl.d_cands), cudaFree(sl.d_queue), cudaFree(sl.d_results);
+        sl.d_blocks = nullptr, sl.d_powers = nullptr, sl.d_fac = nullptr, sl.d_cands = nullptr, sl.d_queue = nullptr, sl.d_results = nullptr;
         if (sl.h_powers) cudaFreeHost(sl.h_powers), sl.h_powers = nullptr;
         CK(cudaMalloc(&sl.d_blocks, nb * N * sizeof(float2)));
         CK(cudaMalloc(&sl.d_powers, nb * 8 * sizeof(float)));
+        CK(cudaMalloc(&sl.d_fac, nb * sizeof(float)));
         CK(cudaMalloc(&sl.d_cands, nb * items * sizeof(CandRec)));
         CK(cudaMalloc(&sl.d_queue, queue_cap * sizeof(QueueRec)));
         CK(cudaMalloc(&sl.d_results, result_cap * sizeof(ResultRec)));
@@ -307,14 +310,23 @@ void msk144_decoder::collect_times() {
     ev_used = 0;
 }
 
-int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
-                                 cudaStream_t st) {
-    EvQuad* evq = nullptr;
-    if (int rc = next_events(&evq)) return rc;
-    cudaEvent_t* ev = evq->e;
-    evq->nb = nb;
-    CK(cudaMemsetAsync(sl.d_counters, 0, 4 * sizeof(int), st));
-    CK(cudaEventRecord(ev[0], st));
+// The front end of one launch group.  With more blocks than SMs the per-block 1/rms (a sequential FP32 sum in the
+// reference, main.cu:301-307) is taken out of the front-end CTAs into rms_kernel, which runs 32 of those chains per warp.
+int msk144_decoder::launch_frontend(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
+                                    cudaStream_t st) {
+    const float* d_fac = nullptr;
+    if (cfg.read_mode == 1 && nb > sm_count) {
+        RmsParams rp;
+        rp.raw = static_cast<const short*>(d_in);
+        rp.chan_stride = chan_stride;
+        rp.bpc = bpc;
+        rp.block0 = block0;
+        rp.nblocks = nb;
+        rp.fac = sl.d_fac;
+        rms_kernel<<<(nb + 31) / 32, 32, 0, st>>>(rp);
+        d_fac = sl.d_fac;
+        launches += 1;
+    }
     if (cfg.read_mode == 1 && cfg.analytic_method == 1) {
         FftParams fp;
         fp.raw = static_cast<const short*>(d_in);
@@ -326,6 +338,7 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
         fp.out = sl.d_blocks;
         fp.powers = sl.d_powers;
         fp.nblocks = nb;
+        fp.fac = d_fac;
         fft_frontend_kernel<<<std::min(nb, sm_count), FFT_THREADS, FFT_SMEM, st>>>(fp);
     } else {
         FrontParams fp;
@@ -336,8 +349,22 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
         fp.block0 = block0;
         fp.out = sl.d_blocks;
         fp.powers = sl.d_powers;
+        fp.fac = d_fac;
         frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, st>>>(fp);
     }
+    CK(cudaGetLastError());
+    return MSK144_OK;
+}
+
+int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stride, int bpc, long long block0, int nb,
+                                 cudaStream_t st) {
+    EvQuad* evq = nullptr;
+    if (int rc = next_events(&evq)) return rc;
+    cudaEvent_t* ev = evq->e;
+    evq->nb = nb;
+    CK(cudaMemsetAsync(sl.d_counters, 0, 4 * sizeof(int), st));
+    CK(cudaEventRecord(ev[0], st));
+    if (int rc = launch_frontend(sl, d_in, chan_stride, bpc, block0, nb, st)) return rc;
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[1], st));
     ScanParams sp;
@@ -518,6 +545,7 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
 extern "C" {
 
 const char* msk144_last_error(void) { return g_err.c_str(); }
+int msk144_fail_(int code, const char* what) { return fail(code, what ? what : ""); }  // for the other translation units
 
 void msk144_config_defaults(msk144_config* cfg) {
     if (!cfg) return;
@@ -859,29 +887,9 @@ int msk144_frontend_host(msk144_decoder* dec, const void* samples, size_t nsampl
     // run only the front-end kernel of each group
     for (int64_t g0 = 0; g0 < total; g0 += group) {
         const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
-        if (dec->cfg.read_mode == 1 && dec->cfg.analytic_method == 1) {
-            FftParams fp;
-            fp.raw = static_cast<const short*>(dec->d_raw);
-            fp.chan_stride = static_cast<long long>(nsamples);
-            fp.bpc = static_cast<int>(total);
-            fp.block0 = g0;
-            fp.twiddle = dec->d_twiddle;
-            fp.hfilt = dec->d_hfilt;
-            fp.out = dec->slot[0].d_blocks;
-            fp.powers = dec->slot[0].d_powers;
-            fp.nblocks = nb;
-            fft_frontend_kernel<<<std::min(nb, dec->sm_count), FFT_THREADS, FFT_SMEM, dec->stream>>>(fp);
-        } else {
-            FrontParams fp;
-            fp.raw = dec->d_raw;
-            fp.chan_stride = static_cast<long long>(nsamples);
-            fp.bpc = static_cast<int>(total);
-            fp.read_mode = dec->cfg.read_mode;
-            fp.block0 = g0;
-            fp.out = dec->slot[0].d_blocks;
-            fp.powers = dec->slot[0].d_powers;
-            frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, dec->stream>>>(fp);
-        }
+        if (int rc = dec->launch_frontend(dec->slot[0], dec->d_raw, static_cast<long long>(nsamples), static_cast<int>(total), g0, nb,
+                                          dec->stream))
+            return rc;
         CK(cudaGetLastError());
         dec->launches += 1;
         if (blocks_re_im)

@@ -461,3 +461,32 @@ def cfg5_channel(channel: int, seconds: float = 60.0):
     n = int(seconds * FS)
     pings = random_pings(rng, n, 20, 1260.0, 1740.0, -4.0, 10.0)
     return audio_stream(pings, n, 1000.0, 1000 + channel), pings
+
+
+def wideband_capture(bins: Sequence[int], decimation: int = 160, seconds: float = 3.0, seed: int = 7, fmt: int = 1,
+                     noise_lsb: float = 3.0, pings_per_channel: int = 3, snr_lo: float = 3.0, snr_hi: float = 10.0):
+    """A wideband I/Q capture at decimation x 12 ksps (rtl_sdr -s 1920000 for 160) with MSK144 pings in the channels
+    `bins` (offset bins[c] x 12 kHz from the centre), white noise of `noise_lsb` per component, quantised to
+    fmt 1 = u8 (rtl_sdr), 2 = s8, 3 = s16 interleaved I,Q.  Returns (capture, {bin: pings})."""
+    from scipy.signal import resample_poly
+    rng = np.random.default_rng(seed)
+    n12 = int(seconds * FS)
+    M = decimation
+    fs_in = M * FS
+    x = noise_lsb * (rng.standard_normal(n12 * M) + 1j * rng.standard_normal(n12 * M))
+    m = np.arange(n12 * M)
+    truth = {}
+    for k in bins:
+        pings = random_pings(rng, n12, pings_per_channel, -40.0, 40.0, snr_lo, snr_hi, frames_lo=4, frames_hi=8)
+        truth[k] = pings
+        amp = lambda p: noise_lsb * np.sqrt(2.0 * 10 ** (p.snr_db / 10) * 2500.0 / fs_in)
+        base = _render(pings, n12, amp)
+        up = resample_poly(base, M, 1)                      # 12 ksps -> M x 12 ksps, unit pass-band gain
+        x += up * np.exp(2j * np.pi * ((k * m) % M) / M)
+    inter = np.empty(2 * len(x))
+    inter[0::2], inter[1::2] = x.real, x.imag
+    if fmt == 1:
+        return np.clip(np.rint(inter + 127.5), 0, 255).astype(np.uint8), truth
+    if fmt == 2:
+        return np.clip(np.rint(inter), -128, 127).astype(np.int8), truth
+    return np.clip(np.rint(inter * 64.0), -32768, 32767).astype(np.int16), truth
