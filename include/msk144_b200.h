@@ -154,8 +154,9 @@ int msk144_get_stage_times(msk144_decoder* dec, msk144_stage_times* t);
  * every complete block, keeps the SNR recurrence, and queues decode lines in output order. */
 int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes);
 /* The same loop for `nchan` channels arriving interleaved (one 2-byte sample of every channel per time step): one
- * overlap buffer and one SNR recurrence per channel; lines carry their channel.  nchan is fixed until
- * msk144_reset_stream().  Do not mix with msk144_push on one decoder. */
+ * overlap buffer and one SNR recurrence per channel; lines carry their channel and come out in time order (block, then
+ * channel), however the caller chunks its pushes.  nchan is fixed until msk144_reset_stream().  Do not mix with
+ * msk144_push on one decoder. */
 int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbytes, int nchan);
 int msk144_poll(msk144_decoder* dec, msk144_line* lines, size_t cap, size_t* nlines);
 int msk144_reset_stream(msk144_decoder* dec);

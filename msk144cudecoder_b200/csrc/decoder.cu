@@ -855,6 +855,11 @@ int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbyte
     for (int c = 0; c < nchan; c++) carry[c] = dec->il_state[c].get();
     if (int rc = dec->decode_common(d_cm, used, nchan, dec->stream, dec->il_next_block, carry.data(), &lv, nullptr))
         return rc;
+    // time order (block, then channel), whatever number of blocks this push happened to complete: the lines of a stream
+    // do not depend on how the caller chunks its pushes
+    std::stable_sort(lv.begin(), lv.end(), [](const msk144_line& a, const msk144_line& b) {
+        return a.block_index != b.block_index ? a.block_index < b.block_index : a.channel < b.channel;
+    });
     for (const auto& l : lv) dec->out_lines.push_back(l);
     dec->il_next_block += static_cast<int64_t>(nblocks);
     dec->il_pending.erase(dec->il_pending.begin(), dec->il_pending.begin() + nblocks * (N / 2) * frame);

@@ -193,7 +193,14 @@ int msk144_pool_push_interleaved(msk144_pool* p, const void* bytes, size_t nbyte
     for (auto& t : th) t.join();
     for (int i = 0; i < n; i++)
         if (part[i].rc != MSK144_OK) return pfail(part[i].rc, "device " + std::to_string(p->device[i]) + ": " + part[i].err);
-    for (int i = 0; i < n; i++) p->out_lines.insert(p->out_lines.end(), part[i].lines.begin(), part[i].lines.end());
+    // members hold contiguous channel ranges in order; (block, channel) order is what one decoder's
+    // msk144_push_interleaved emits, independent of how the pushes were chunked
+    std::vector<msk144_line> merged;
+    for (int i = 0; i < n; i++) merged.insert(merged.end(), part[i].lines.begin(), part[i].lines.end());
+    std::stable_sort(merged.begin(), merged.end(), [](const msk144_line& a, const msk144_line& b) {
+        return a.block_index != b.block_index ? a.block_index < b.block_index : a.channel < b.channel;
+    });
+    p->out_lines.insert(p->out_lines.end(), merged.begin(), merged.end());
     return MSK144_OK;
 }
 

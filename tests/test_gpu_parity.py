@@ -337,6 +337,12 @@ def test_multichannel_streaming_equals_single_channel_streams(gpu, synth):
             d.push(il[:64], nchan=nch + 1)               # the channel count is fixed in mid-stream
     key = lambda ls: sorted((l["channel"],) + lines_key([l])[0] for l in ls)
     assert len(want) > 0 and key(got) == key(want)
+    # time order (block, then channel), and the same sequence whatever the chunking: one push of everything
+    order = [(l["block"], l["channel"]) for l in got]
+    assert order == sorted(order)
+    with gpu.Decoder(compat_cache=True, **kw) as d:
+        d.push(il, nchan=nch)
+        assert d.poll(4096) == got
     p = subprocess.run([gpu.CLI_PATH, "--search-width=100", "--scan-depth=3", "--nbadsync-threshold=2", f"--channels={nch}"],
                        input=il, capture_output=True)
     out = p.stdout.decode().splitlines()
