@@ -1,9 +1,11 @@
 """The channeliser in front of the decoder (msk144_channelizer_*): wideband I/Q -> channels of 12 ksps s8 I/Q.
 
 CPU: the numpy oracle's two independent forms agree, the prototype filter meets its stated response, streaming history.
-GPU: the CUDA kernel against the oracle (s8 output: equal except for roundings that sit on a .5 boundary within FP32
-accuracy -- counted, printed and bounded), every kernel instantiation class (branches per lane 1..8, 1/2/4/8 channels per
-group), both output layouts, streaming == one shot, and capture -> channeliser -> decoder end to end."""
+CPU: the Stockham stages of csrc/chz_fft.h against a direct DFT for every decimation that has a plan (host harness).
+GPU: the CUDA kernels against the oracle (s8 output: equal except for roundings that sit on a .5 boundary within FP32
+accuracy -- counted, printed and bounded), both kernels (direct: 1/2/4 channels per group; FFT across the branches with
+every radix), all three input formats, both output layouts, unaligned input, streaming == one shot, and capture ->
+channeliser -> decoder end to end."""
 import numpy as np
 import pytest
 
@@ -47,6 +49,21 @@ def test_prototype_response():
     assert db(f >= 10000).max() < -79.0           # everything that folds onto |f| < 2 kHz
 
 
+def test_fft_stages_against_direct_dft(tmp_path):
+    """csrc/chz_fft.h compiles as plain C++: every stage is walked thread index by thread index on the host."""
+    import os
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cuda_inc = os.path.join(os.environ.get("CUDA_HOME", "/usr/local/cuda"), "include")
+    exe = str(tmp_path / "chz_fft_host")
+    subprocess.run(["g++", "-O2", "-std=c++17", f"-I{cuda_inc}", os.path.join(root, "tests", "chz_fft_host.cpp"), "-o", exe], check=True)
+    r = subprocess.run([exe], capture_output=True, text=True)
+    rows = [l.split() for l in r.stdout.splitlines()]
+    assert r.returncode == 0, r.stdout[-400:]
+    assert len(rows) >= 100 and {"160", "256", "200", "33", "91"} <= {row[0] for row in rows}
+    assert max(float(row[2]) for row in rows) < 5e-7
+
+
 def lsb_report(name, got, want):
     d = np.abs(got.astype(np.int32) - want.astype(np.int32))
     frac = float((d > 0).mean())
@@ -57,15 +74,20 @@ def lsb_report(name, got, want):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("M,fmt,bins,gain", [
-    (160, 1, [0, 5, -17, 40, 79], 8.0),          # the README's rate; 5 branches per lane, groups of 4
-    (160, 1, [3], 8.0),                          # one channel (the README's chain)
-    (2, 2, [0, 1], 1.0),                         # smallest decimation
-    (20, 3, [0, -3, 7], 0.9),                    # 240 ksps s16
+    (160, 1, [0, 5, -17, 40], 8.0),               # the README's rate; direct kernel, 4 channels
+    (160, 1, [3], 8.0),                           # one channel (the README's chain)
+    (160, 1, list(range(-80, 80)), 8.0),          # every channel of the capture: FFT across the branches, 8 x 4 x 5
+    (2, 2, [0, 1], 1.0),                          # smallest decimation
+    (20, 3, [0, -3, 7], 0.9),                     # 240 ksps s16
     (80, 2, [1, 2], 2.0),
-    (100, 1, [0, 1, 2, 3, 4, 5, 6, 7, -1], 8.0),  # 9 channels: a full group of 8 and a padded one
-    (200, 2, [0, -99, 64, 13], 6.0),             # 2.4 Msps, 7 branches per lane
-    (256, 1, list(range(-8, 8)), 12.0),          # 3.072 Msps, 8 branches per lane, two full groups
-    (33, 3, [0, 16, -16], 0.9),                  # a decimation that is not a multiple of anything
+    (100, 1, [0, 1, 2, 3, 4, 5, 6, 7, -1], 8.0),  # FFT 4 x 5 x 5
+    (200, 2, [0, -99, 64, 13], 6.0),              # 2.4 Msps
+    (256, 1, list(range(-8, 8)), 12.0),           # 3.072 Msps, FFT 8 x 8 x 4
+    (256, 3, list(range(-128, 128)), 12.0),       # s16, every channel
+    (33, 3, [0, 16, -16], 0.9),                   # a decimation that is not a multiple of anything
+    (33, 2, [0, 16, -16, 1, 2, 3, -5], 0.9),      # FFT 3 x 11 (dense radix 11)
+    (91, 2, list(range(10)), 2.0),                # FFT 7 x 13
+    (34, 1, [0, 1, -1, 16, -16, 5], 4.0),         # 2 x 17: no FFT plan, two groups of the direct kernel
 ])
 def test_gpu_channelizer_matches_oracle(product, M, fmt, bins, gain):
     rng = np.random.default_rng(M * 7 + fmt)
@@ -84,9 +106,10 @@ def test_gpu_channelizer_matches_oracle(product, M, fmt, bins, gain):
 
 
 @pytest.mark.gpu
-def test_gpu_channelizer_streaming_and_layouts(product):
+@pytest.mark.parametrize("bins", [[0, 5, -17], [0, 5, -17, 40, 79, -80]])   # direct kernel / FFT kernel
+def test_gpu_channelizer_streaming_and_layouts(product, bins):
     import torch
-    M, bins, fmt = 160, [0, 5, -17], 1
+    M, fmt = 160, 1
     rng = np.random.default_rng(5)
     nframes = 4000
     cap = random_capture(rng, nframes, M, fmt)
@@ -119,6 +142,14 @@ def test_gpu_channelizer_streaming_and_layouts(product):
         assert np.array_equal(d_cm.cpu().numpy()[:, :nframes], whole)
         assert np.array_equal(d_tm.cpu().numpy().transpose(1, 0, 2), whole)
         assert np.array_equal(d_late.cpu().numpy()[:, :nframes - 1000], whole[:, 1000:])
+        # an input pointer that is not 16-byte aligned (the staging copies are): same bytes, same answer
+        d_off = torch.zeros(cap.size + 64, dtype=torch.uint8, device="cuda")
+        for shift in (2, 6, 14):
+            d_off[shift:shift + cap.size] = d_in
+            d_cm.zero_()
+            z.channelize_device(d_off.data_ptr() + shift, nframes, d_cm.data_ptr(), stride, 1, 0, s.cuda_stream)
+            torch.cuda.synchronize()
+            assert np.array_equal(d_cm.cpu().numpy()[:, :nframes], whole), shift
         with pytest.raises(product.Msk144Error):
             z.channelize_device(d_in.data_ptr(), nframes, d_cm.data_ptr(), stride, 1, 8, s.cuda_stream)
     for bad in (dict(decimation=1, bins=[0]), dict(decimation=257, bins=[0]), dict(decimation=160, bins=[160]),

@@ -2,7 +2,7 @@
 """Channeliser throughput on one GPU: resident u8 capture at 1.92 Msps (the README's rtl_sdr rate), CUDA events on the
 launching stream, input larger than L2.  One JSON line per channel count with the HBM and FP32 rooflines:
   bytes  = capture bytes read once + channel bytes written once            (algorithmic)
-  flops  = frames x (2 x 2 x 8 M [branch filters, once per channel group] + 8 M per channel [DFT row])"""
+  flops  = frames x (32 M [branch filters] + 8 M per channel [direct kernel] or 5 M log2 M [FFT kernel, > 4 channels])"""
 import json
 import os
 import sys
@@ -26,7 +26,10 @@ def main():
     g = torch.Generator(device="cuda").manual_seed(1)
     cap = torch.randint(96, 160, (nframes * M * 2,), dtype=torch.uint8, device="cuda", generator=g)
     stride = (nframes + 7) // 8 * 8
+    only = [int(v) for v in sys.argv[2].split(",")] if len(sys.argv) > 2 else None
     for bins in ([0], [0, 5], [0, 5, -17, 40], list(range(8)), list(range(-16, 16)), list(range(-80, 80))):
+        if only and len(bins) not in only:
+            continue
         nchan = len(bins)
         out = torch.zeros((nchan, stride, 2), dtype=torch.int8, device="cuda")
         with m.Channelizer(M, bins, gain=8.0) as z:
@@ -42,16 +45,18 @@ def main():
             e1.record(s)
             torch.cuda.synchronize()
             ms = e0.elapsed_time(e1) / reps
-        nch = 8 if nchan >= 8 else 4 if nchan > 2 else nchan
-        groups = (nchan + nch - 1) // nch
+        fft = nchan > 4
+        nch = 4 if nchan > 2 else nchan
+        groups = 1 if fft else (nchan + nch - 1) // nch
         bytes_alg = cap.numel() + nchan * nframes * 2
-        flops = nframes * (groups * 2 * 2 * 8 * M + groups * nch * 8 * M)
+        # branch filters 16 FMA per sample; direct: 4 FMA per (sample, channel); FFT 8 x 4 x 5: ~5 M log2 M real operations
+        flops = nframes * (2 * 16 * M + (5 * M * np.log2(M) if fft else 8 * M * nchan))
         print(json.dumps({"bench": "channelizer", "lib": os.path.basename(m.LIB_PATH), "decimation": M, "input": "u8 I/Q 1.92 Msps",
                           "seconds_of_capture": seconds, "channels": nchan, "ms": ms, "x_realtime": seconds / (ms * 1e-3),
                           "input_msps": nframes * M / ms / 1e3,
                           "roofline": {"bound": "hbm", "achieved": bytes_alg / ms / 1e6, "peak": hbm_peak, "unit": "GB/s",
                                        "frac": bytes_alg / ms / 1e6 / hbm_peak},
-                          "fp32": {"achieved": flops / ms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s", "frac": flops / ms / 1e9 / fp32_peak},
+                          "kernel": "fft" if fft else "direct", "fp32": {"achieved": flops / ms / 1e9, "peak": fp32_peak, "unit": "TFLOP/s", "frac": flops / ms / 1e9 / fp32_peak},
                           "checksum": int(out.to(torch.int32).sum().item())}), flush=True)
 
 

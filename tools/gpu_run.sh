@@ -35,6 +35,11 @@ for step in "$@"; do
       done; ls -la gpurun_out/prof_front_*.ncu-rep ;;
     chz) timeout 900 python -m pytest tests/test_channelizer.py -m gpu -q -s --timeout=600 > gpurun_out/pytest_chz.log 2>&1; echo "chz rc=$?"; grep -E "differ|bin |passed|failed|Error|error" gpurun_out/pytest_chz.log | tail -30
          timeout 600 python tools/bench_channelizer.py > gpurun_out/chz_bench.jsonl 2> gpurun_out/chz_bench.err; cut -c1-500 gpurun_out/chz_bench.jsonl; tail -3 gpurun_out/chz_bench.err ;;
+    ncu_chz)
+      for n in 1 160; do
+        ncu --set full --clock-control none --import-source on -k regex:'direct_kernel|fft_kernel' -s 5 -c 1 -f -o gpurun_out/prof_chz_$n python tools/bench_channelizer.py 120 $n > gpurun_out/ncu_chz_$n.log 2>&1
+        echo "ncu_chz $n rc=$?"
+      done; ls -la gpurun_out/prof_chz_*.ncu-rep ;;
     warpops) ./scratch/warpops > gpurun_out/warpops.txt 2>&1; cat gpurun_out/warpops.txt ;;
     scanprof) for so in scratch/variants_prof/*.so; do echo "== $so"; MSK144_B200_LIB=$PWD/$so timeout 300 python tools/scan_prof.py 2>&1 | tail -20; done > gpurun_out/scanprof.log 2>&1; cat gpurun_out/scanprof.log ;;
     golden_multi) timeout 1500 python -m pytest tests/test_golden.py tests/test_gpu_multi.py -m gpu -q --timeout=900 -s > gpurun_out/pytest_gm.log 2>&1; echo "golden_multi rc=$?"; grep -E "passed|failed|_60s:|Error" gpurun_out/pytest_gm.log | tail -20 ;;
