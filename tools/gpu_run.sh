@@ -28,6 +28,14 @@ for step in "$@"; do
       $CMD > gpurun_out/ncu_plain2.log 2>&1 &&
       ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 0 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
       echo "ncu_full rc=$?"; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/*.ncu-rep ;;
+    ncu_scan)
+      CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
+      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel' -s 0 -c 1 -f -o gpurun_out/prof_scan $CMD > gpurun_out/ncu_scan.log 2>&1
+      echo "ncu_scan rc=$?"; tail -2 gpurun_out/ncu_scan.log; ls -la gpurun_out/prof_scan.ncu-rep ;;
+    ncu_ldpc)
+      CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
+      ncu --set full --clock-control none --import-source on -k regex:'ldpc_kernel' -s 0 -c 1 -f -o gpurun_out/prof_ldpc $CMD > gpurun_out/ncu_ldpc.log 2>&1
+      echo "ncu_ldpc rc=$?"; tail -2 gpurun_out/ncu_ldpc.log; ls -la gpurun_out/prof_ldpc.ncu-rep ;;
     ncu_front)
       for v in cur cur_fft; do
         MSK144_B200_LIB=$PWD/scratch/variants/$v.so ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 4 -c 2 -f -o gpurun_out/prof_front_$v python tools/bench_stages.py frontend > gpurun_out/ncu_front_$v.log 2>&1
