@@ -56,7 +56,12 @@ enum {
      * of unsatisfied checks has not decreased for three checks running (iter >= 5, more than 10 unsatisfied), optional
      * a-priori mask (msk144_set_ap_mask).  Same arithmetic.  Off by default: the drop-in output is the reference's.
      * bpdecode128_90.f90 is not on this box; the mode is restated from the published algorithm (parity unpinned). */
-    MSK144_FLAG_WSJTX_BP = 4
+    MSK144_FLAG_WSJTX_BP = 4,
+    /* Host threads waiting for the GPU sleep instead of spinning: msk144_create sets cudaDeviceScheduleBlockingSync on the
+     * decoder's device, as the reference does for its whole process (main.cu:115).  For live use (one 216 ms hop per push,
+     * the GPU busy for a fraction of a millisecond); costs a few tens of microseconds of wake-up latency per poll, so the
+     * batch entry points leave it off.  The CLI sets it. */
+    MSK144_FLAG_BLOCKING_SYNC = 8
 };
 
 /* The seven CLI values of main.cu:124-133 + placement.  Zero-initialise, then msk144_config_defaults(). */

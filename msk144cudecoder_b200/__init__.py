@@ -25,6 +25,7 @@ BLOCK_SAMPLES, HOP_SAMPLES = 5184, 2592
 FLAG_COMPAT_DECODE_CACHE = 1
 FLAG_SKIP_WAV_HEADER = 2
 FLAG_WSJTX_BP = 4
+FLAG_BLOCKING_SYNC = 8
 
 EXPORTED_SYMBOLS = [
     "msk144_last_error", "msk144_config_defaults", "msk144_create", "msk144_destroy", "msk144_get_info",

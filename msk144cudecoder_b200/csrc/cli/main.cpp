@@ -58,7 +58,7 @@ static const char* mode_string(int m) {
 int main(int argc, char* const argv[]) {
     msk144_config cfg;
     msk144_config_defaults(&cfg);
-    cfg.flags = MSK144_FLAG_COMPAT_DECODE_CACHE;
+    cfg.flags = MSK144_FLAG_COMPAT_DECODE_CACHE | MSK144_FLAG_BLOCKING_SYNC;  // main.cu:437-445, main.cu:115
     bool center_set = false, json = false;
     int dedupe_gap = -1;  // < 0: print every per-block line, as the reference does
     int nchan = 1;

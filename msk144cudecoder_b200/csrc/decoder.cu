@@ -574,6 +574,10 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
         return fail(MSK144_ENODEV, "no CUDA device: this library has no CPU path");
     if (cfg->device < 0 || cfg->device >= ndev) return fail(MSK144_EINVAL, "bad device ordinal");
     CK(cudaSetDevice(cfg->device));
+    if (cfg->flags & MSK144_FLAG_BLOCKING_SYNC) {
+        // main.cu:115.  A device whose context another part of the process already configured keeps its setting.
+        if (cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess) cudaGetLastError();
+    }
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cfg->device));
     if (prop.major < 10)

@@ -41,6 +41,10 @@ for step in "$@"; do
         MSK144_B200_LIB=$PWD/scratch/variants/$v.so ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 4 -c 2 -f -o gpurun_out/prof_front_$v python tools/bench_stages.py frontend > gpurun_out/ncu_front_$v.log 2>&1
         echo "ncu_front $v rc=$?"
       done; ls -la gpurun_out/prof_front_*.ncu-rep ;;
+    ncu_fft)
+      timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
+      echo "ncu_fft rc=$?"; ls -la gpurun_out/prof_front.ncu-rep ;;
     chz) timeout 900 python -m pytest tests/test_channelizer.py -m gpu -q -s --timeout=600 > gpurun_out/pytest_chz.log 2>&1; echo "chz rc=$?"; grep -E "differ|bin |passed|failed|Error|error" gpurun_out/pytest_chz.log | tail -30
          timeout 600 python tools/bench_channelizer.py > gpurun_out/chz_bench.jsonl 2> gpurun_out/chz_bench.err; cut -c1-500 gpurun_out/chz_bench.jsonl; tail -3 gpurun_out/chz_bench.err ;;
     ncu_chz)
