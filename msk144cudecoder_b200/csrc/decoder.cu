@@ -101,8 +101,26 @@ ScanEntry scan_entry(int depth) {
                                      scan_kernel<5>, scan_kernel<6>, scan_kernel<7>, scan_kernel<8>};
     return tab[std::max(1, std::min(8, depth)) - 1];
 }
+ScanEntry scan2_entry(int depth) {
+    static const ScanEntry tab[8] = {scan2_kernel<1>, scan2_kernel<2>, scan2_kernel<3>, scan2_kernel<4>,
+                                     scan2_kernel<5>, scan2_kernel<6>, scan2_kernel<7>, scan2_kernel<8>};
+    return tab[std::max(1, std::min(8, depth)) - 1];
+}
+// MSK144_SCAN_FORM=2 selects the second form of the kernel (scan2.cuh: two 448-thread CTAs per SM, 110 KB each); the
+// default is the first form (one 864-thread CTA per SM), 1 % faster on the deep scan (profiles/r02_scan_notes.md).
+// Both produce the same bits; the GPU tests run under either.
+bool scan_form2() {
+    static const bool v = [] {
+        const char* e = std::getenv("MSK144_SCAN_FORM");
+        return e && std::atoi(e) == 2;
+    }();
+    return v;
+}
 void launch_scan(int depth, dim3 grid, cudaStream_t st, const ScanParams& sp) {
-    scan_entry(depth)<<<grid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
+    if (scan_form2())
+        scan2_entry(depth)<<<grid, SCAN2_THREADS, SCAN2_SMEM, st>>>(sp);
+    else
+        scan_entry(depth)<<<grid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
 }
 
 struct RawResult {
@@ -610,6 +628,8 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
     CKD(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
     CKD(cudaFuncSetAttribute(fft_frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FFT_SMEM)));
     CKD(cudaFuncSetAttribute(scan_entry(d->depth), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN_SMEM)));
+    CKD(cudaFuncSetAttribute(scan2_entry(d->depth), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(SCAN2_SMEM)));
+    CKD(cudaFuncSetAttribute(scan2_entry(d->depth), cudaFuncAttributePreferredSharedMemoryCarveout, 100));
     {
         // mixer table, once per decoder (scan_kernel.cuh:45-69 evaluates it per block and frequency)
         const size_t bytes = static_cast<size_t>(d->nf) * N * sizeof(float2);

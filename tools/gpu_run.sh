@@ -26,11 +26,11 @@ for step in "$@"; do
     ncu_full)
       CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
       $CMD > gpurun_out/ncu_plain2.log 2>&1 &&
-      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel|ldpc_kernel|frontend_kernel' -s 0 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
+      ncu --set full --clock-control none --import-source on -k regex:'scan2?_kernel|ldpc_kernel|frontend_kernel' -s 0 -c 3 -f -o gpurun_out/prof_full $CMD > gpurun_out/ncu_full.log 2>&1
       echo "ncu_full rc=$?"; tail -3 gpurun_out/ncu_full.log; ls -la gpurun_out/*.ncu-rep ;;
     ncu_scan)
       CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
-      ncu --set full --clock-control none --import-source on -k regex:'scan_kernel' -s 0 -c 1 -f -o gpurun_out/prof_scan $CMD > gpurun_out/ncu_scan.log 2>&1
+      ncu --set full --clock-control none --import-source on -k regex:'scan2?_kernel' -s 0 -c 1 -f -o gpurun_out/prof_scan $CMD > gpurun_out/ncu_scan.log 2>&1
       echo "ncu_scan rc=$?"; tail -2 gpurun_out/ncu_scan.log; ls -la gpurun_out/prof_scan.ncu-rep ;;
     ncu_ldpc)
       CMD="python bench.py --steps 1 --warmup 1 --seconds 30 --no-cpu-baseline"
@@ -41,9 +41,13 @@ for step in "$@"; do
         MSK144_B200_LIB=$PWD/scratch/variants/$v.so ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 4 -c 2 -f -o gpurun_out/prof_front_$v python tools/bench_stages.py frontend > gpurun_out/ncu_front_$v.log 2>&1
         echo "ncu_front $v rc=$?"
       done; ls -la gpurun_out/prof_front_*.ncu-rep ;;
+    ab_scan)
+      for f in 2 1 2 1; do MSK144_SCAN_FORM=$f timeout 300 python tools/bench_stages.py scan 2>&1 | sed "s/^/form$f /" ; done > gpurun_out/ab_scan.log 2>&1; cut -c1-330 gpurun_out/ab_scan.log ;;
+    parity12)
+      for f in 1 2; do MSK144_SCAN_FORM=$f timeout 900 python -m pytest tests/test_golden.py tests/test_gpu_parity.py -m gpu -q -x --timeout=600 > gpurun_out/pytest_form$f.log 2>&1; echo "form $f rc=$?"; tail -3 gpurun_out/pytest_form$f.log; done ;;
     ncu_fft)
       timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -s 6 -c 40 -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
       echo "ncu_fft rc=$?"; ls -la gpurun_out/prof_front.ncu-rep ;;
     chz) timeout 900 python -m pytest tests/test_channelizer.py -m gpu -q -s --timeout=600 > gpurun_out/pytest_chz.log 2>&1; echo "chz rc=$?"; grep -E "differ|bin |passed|failed|Error|error" gpurun_out/pytest_chz.log | tail -30
          timeout 600 python tools/bench_channelizer.py > gpurun_out/chz_bench.jsonl 2> gpurun_out/chz_bench.err; cut -c1-500 gpurun_out/chz_bench.jsonl; tail -3 gpurun_out/chz_bench.err ;;
@@ -53,7 +57,11 @@ for step in "$@"; do
         echo "ncu_chz $n rc=$?"
       done; ls -la gpurun_out/prof_chz_*.ncu-rep ;;
     warpops) ./scratch/warpops > gpurun_out/warpops.txt 2>&1; cat gpurun_out/warpops.txt ;;
-    scanprof) for so in scratch/variants_prof/*.so; do echo "== $so"; MSK144_B200_LIB=$PWD/$so timeout 300 python tools/scan_prof.py 2>&1 | tail -20; done > gpurun_out/scanprof.log 2>&1; cat gpurun_out/scanprof.log ;;
+    scanprof) for so in scratch/variants_prof/*.so; do for f in 1 2; do echo "== $so form $f"; MSK144_SCAN_FORM=$f MSK144_B200_LIB=$PWD/$so timeout 300 python tools/scan_prof.py 2>&1 | tail -20; done; done > gpurun_out/scanprof.log 2>&1; cat gpurun_out/scanprof.log ;;
+    ab_scan_variants)
+      for rep in 1 2; do for so in scratch/variants/*.so; do for f in 1 2; do
+        MSK144_SCAN_FORM=$f MSK144_B200_LIB=$PWD/$so timeout 300 python tools/bench_stages.py scan 2>&1 | grep stages_deep | sed "s/^/form$f /"
+      done; done; done > gpurun_out/ab_scan_variants.log 2>&1; cut -c1-260 gpurun_out/ab_scan_variants.log ;;
     golden_multi) timeout 1500 python -m pytest tests/test_golden.py tests/test_gpu_multi.py -m gpu -q --timeout=900 -s > gpurun_out/pytest_gm.log 2>&1; echo "golden_multi rc=$?"; grep -E "passed|failed|_60s:|Error" gpurun_out/pytest_gm.log | tail -20 ;;
     *) echo "unknown step $step" ;;
   esac
