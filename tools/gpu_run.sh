@@ -45,6 +45,13 @@ for step in "$@"; do
       for f in 2 1 2 1; do MSK144_SCAN_FORM=$f timeout 300 python tools/bench_stages.py scan 2>&1 | sed "s/^/form$f /" ; done > gpurun_out/ab_scan.log 2>&1; cut -c1-330 gpurun_out/ab_scan.log ;;
     parity12)
       for f in 1 2; do MSK144_SCAN_FORM=$f timeout 900 python -m pytest tests/test_golden.py tests/test_gpu_parity.py -m gpu -q -x --timeout=600 > gpurun_out/pytest_form$f.log 2>&1; echo "form $f rc=$?"; tail -3 gpurun_out/pytest_form$f.log; done ;;
+    scale8)   # on an 8-GPU box: in-process pool 1/2/4/8, then bench.py under torchrun at N = 8 and N = 4 (cfg2 replicas + cfg5 gather)
+      nvidia-smi -L > gpurun_out/gpus.txt 2>&1
+      timeout 600 python tools/bench_pool.py 256 > gpurun_out/pool_scale.jsonl 2> gpurun_out/pool_scale.err; echo "pool rc=$?"; cut -c1-420 gpurun_out/pool_scale.jsonl; tail -3 gpurun_out/pool_scale.err
+      for n in 8 4; do
+        timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 3 --warmup 3 --no-cli --no-cpu-baseline > gpurun_out/bench_n$n.log 2> gpurun_out/bench_n$n.err
+        echo "bench n=$n rc=$?"; tail -1 gpurun_out/bench_n$n.log | cut -c1-300; tail -3 gpurun_out/bench_n$n.err
+      done ;;
     ncu_fft)
       timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
       timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -s 6 -c 40 -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
