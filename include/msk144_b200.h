@@ -179,6 +179,12 @@ int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t samp
                          void* stream, msk144_line* lines, size_t line_cap, size_t* nlines,
                          msk144_result* results, size_t result_cap, size_t* nresults);
 
+/* The complete output of the decoder's most recent msk144_decode_* call, which it keeps until the next one: after
+ * MSK144_EOVERFLOW (counts returned, arrays too small) call this with arrays of the reported sizes instead of decoding
+ * again.  Either array may be NULL. */
+int msk144_last_output(msk144_decoder* dec, msk144_line* lines, size_t line_cap, size_t* nlines,
+                       msk144_result* results, size_t result_cap, size_t* nresults);
+
 /* Multi-channel input as a channeliser / multi-receiver front end delivers it: one sample of every channel per time
  * step (samples[t][c], 2 bytes each).  The reference reads one channel from stdin (main.cu:261-298); this is the ingest
  * adapter of SURVEY.md section 8f.  `_device`: transposes d_in [spc][nchan] into d_out [nchan][spc] (the layout of
@@ -280,6 +286,9 @@ msk144_decoder* msk144_pool_member(msk144_pool* pool, int32_t i); /* for msk144_
 /* == msk144_decode_host over all members */
 int msk144_pool_decode_host(msk144_pool* pool, const void* samples, size_t samples_per_channel, int nchan,
                             msk144_line* lines, size_t line_cap, size_t* nlines,
+                            msk144_result* results, size_t result_cap, size_t* nresults);
+/* == msk144_last_output: the merged output of the pool's most recent msk144_pool_decode_host */
+int msk144_pool_last_output(msk144_pool* pool, msk144_line* lines, size_t line_cap, size_t* nlines,
                             msk144_result* results, size_t result_cap, size_t* nresults);
 /* == msk144_push_interleaved / msk144_poll / msk144_reset_stream over all members; nbytes must be a whole number of
  * time steps (2 * nchan bytes each) */

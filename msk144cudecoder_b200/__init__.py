@@ -153,6 +153,8 @@ def lib():
         L.msk144_pool_member.argtypes = [vp, C.c_int32]
         L.msk144_pool_member.restype = vp
         L.msk144_pool_decode_host.argtypes = L.msk144_decode_host.argtypes
+        L.msk144_last_output.argtypes = [vp, C.POINTER(Line), sz, C.POINTER(sz), vp, sz, C.POINTER(sz)]
+        L.msk144_pool_last_output.argtypes = L.msk144_last_output.argtypes
         L.msk144_pool_push_interleaved.argtypes = [vp, vp, sz, C.c_int]
         L.msk144_pool_poll.argtypes = [vp, C.POINTER(Line), sz, C.POINTER(sz)]
         L.msk144_pool_reset_stream.argtypes = [vp]
@@ -231,9 +233,13 @@ class Decoder:
         nl, nr = C.c_size_t(0), C.c_size_t(0)
         rc = fn(self._h, ptr, spc, nchan, *extra, lines, line_cap, C.byref(nl),
                 results.ctypes.data if result_cap else None, result_cap, C.byref(nr) if result_cap else None)
-        if rc == -5 and (nl.value > line_cap or nr.value > result_cap):  # grow and retry once
-            return self._decode(fn, ptr, spc, nchan, extra, max(line_cap, nl.value),
-                                max(result_cap, nr.value) if result_cap else 0)
+        if rc == -5 and (nl.value > line_cap or nr.value > result_cap):
+            # the decoder keeps its output: fetch it into arrays of the reported sizes (no second decode)
+            line_cap, result_cap = max(line_cap, nl.value), (max(result_cap, nr.value) if result_cap else 0)
+            lines = (Line * line_cap)()
+            results = np.zeros(result_cap, RESULT_DTYPE)
+            rc = lib().msk144_last_output(self._h, lines, line_cap, C.byref(nl), results.ctypes.data if result_cap else None,
+                                          result_cap, C.byref(nr) if result_cap else None)
         _check(rc)
         return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
 
@@ -381,18 +387,21 @@ class Pool:
     def decode_host(self, samples: np.ndarray, nchan: int, line_cap: int = 4096, result_cap: int = 0):
         samples = np.ascontiguousarray(samples)
         spc = samples.nbytes // 2 // nchan
-        while True:
+        lines = (Line * line_cap)()
+        results = np.zeros(result_cap, RESULT_DTYPE)
+        nl, nr = C.c_size_t(0), C.c_size_t(0)
+        rc = lib().msk144_pool_decode_host(self._h, samples.ctypes.data, spc, nchan, lines, line_cap, C.byref(nl),
+                                           results.ctypes.data if result_cap else None, result_cap,
+                                           C.byref(nr) if result_cap else None)
+        if rc == -5 and (nl.value > line_cap or nr.value > result_cap):  # the pool keeps its output: no second decode
+            line_cap, result_cap = max(line_cap, nl.value), (max(result_cap, nr.value) if result_cap else 0)
             lines = (Line * line_cap)()
             results = np.zeros(result_cap, RESULT_DTYPE)
-            nl, nr = C.c_size_t(0), C.c_size_t(0)
-            rc = lib().msk144_pool_decode_host(self._h, samples.ctypes.data, spc, nchan, lines, line_cap, C.byref(nl),
+            rc = lib().msk144_pool_last_output(self._h, lines, line_cap, C.byref(nl),
                                                results.ctypes.data if result_cap else None, result_cap,
                                                C.byref(nr) if result_cap else None)
-            if rc == -5 and (nl.value > line_cap or nr.value > result_cap):
-                line_cap, result_cap = max(line_cap, nl.value), (max(result_cap, nr.value) if result_cap else 0)
-                continue
-            self._check(rc)
-            return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
+        self._check(rc)
+        return [_line_dict(lines[i]) for i in range(nl.value)], results[:nr.value].copy()
 
     def push(self, data: bytes, nchan: int):
         self._check(lib().msk144_pool_push_interleaved(self._h, data, len(data), nchan))

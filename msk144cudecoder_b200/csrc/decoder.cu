@@ -178,6 +178,15 @@ struct msk144_decoder {
     cudaStream_t copy_stream = nullptr;
     void* d_raw = nullptr;
     size_t d_raw_bytes = 0;
+    // msk144_decode_host: the input goes up in pieces on its own stream while the first launch groups already run; a
+    // group waits for the piece that holds its last sample (pieces and groups both advance through d_raw in order)
+    static constexpr size_t UP_PIECE = 8u << 20;
+    cudaStream_t up_stream = nullptr;
+    std::vector<cudaEvent_t> up_ev;
+    size_t up_pieces = 0;  // pieces in flight for the current call (0: input already resident)
+    long long up_waited = -1;
+    int upload_pieces(const void* h_src, size_t bytes);
+    int wait_for_input(size_t end_byte, cudaStream_t st);
     float2* d_twiddle = nullptr;
     float* d_hfilt = nullptr;
     unsigned short* d_edge_tab = nullptr;
@@ -203,6 +212,8 @@ struct msk144_decoder {
     int64_t next_block = 0;
     ChanState stream_state;
     std::deque<msk144_line> out_lines;
+    std::vector<msk144_line> last_lines;      // output of the most recent batch decode (msk144_last_output)
+    std::vector<msk144_result> last_results;
 
     ~msk144_decoder() { release(); }
     void release();
@@ -256,6 +267,9 @@ void msk144_decoder::release() {
     ev_used = 0;
     if (stream) cudaStreamDestroy(stream), stream = nullptr;
     if (copy_stream) cudaStreamDestroy(copy_stream), copy_stream = nullptr;
+    for (auto& e : up_ev) cudaEventDestroy(e);
+    up_ev.clear();
+    if (up_stream) cudaStreamDestroy(up_stream), up_stream = nullptr;
     cap_blocks = 0;
 }
 
@@ -289,6 +303,34 @@ int msk144_decoder::ensure_raw(size_t bytes) {
     d_raw = nullptr, d_raw_bytes = 0;
     CK(cudaMalloc(&d_raw, bytes));
     d_raw_bytes = bytes;
+    return 0;
+}
+
+int msk144_decoder::upload_pieces(const void* h_src, size_t bytes) {
+    if (!up_stream) CK(cudaStreamCreateWithFlags(&up_stream, cudaStreamNonBlocking));
+    up_pieces = (bytes + UP_PIECE - 1) / UP_PIECE;
+    up_waited = -1;
+    while (up_ev.size() < up_pieces) {
+        cudaEvent_t e;
+        CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        up_ev.push_back(e);
+    }
+    for (size_t i = 0; i < up_pieces; i++) {
+        const size_t off = i * UP_PIECE, len = std::min(UP_PIECE, bytes - off);
+        CK(cudaMemcpyAsync(static_cast<char*>(d_raw) + off, static_cast<const char*>(h_src) + off, len, cudaMemcpyHostToDevice, up_stream));
+        CK(cudaEventRecord(up_ev[i], up_stream));
+    }
+    h2d_bytes += bytes;
+    return 0;
+}
+
+int msk144_decoder::wait_for_input(size_t end_byte, cudaStream_t st) {
+    if (up_pieces == 0 || end_byte == 0) return 0;
+    const long long piece = static_cast<long long>(std::min((end_byte - 1) / UP_PIECE, up_pieces - 1));
+    if (piece > up_waited) {
+        CK(cudaStreamWaitEvent(st, up_ev[static_cast<size_t>(piece)], 0));
+        up_waited = piece;
+    }
     return 0;
 }
 
@@ -544,6 +586,11 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
     int prev_nb = 0, cur = 0;
     for (int64_t g0 = 0; g0 < total; g0 += group) {
         const int nb = static_cast<int>(std::min<int64_t>(group, total - g0));
+        {
+            const int64_t gl = g0 + nb - 1;  // last block of the group: channel gl / bpc, block gl % bpc of it
+            const size_t end_sample = static_cast<size_t>(gl / bpc) * spc + static_cast<size_t>(gl % bpc) * (N / 2) + N;
+            if (int rc = wait_for_input(end_sample * 2, st)) return rc;
+        }
         if (int rc = launch_group(slot[cur], d_in, static_cast<long long>(spc), static_cast<int>(bpc), g0, nb, st)) return rc;
         if (prev_g0 >= 0) {
             if (int rc = fetch_group(slot[cur ^ 1], prev_nb, &raw, prev_g0, &powers)) return rc;
@@ -737,6 +784,16 @@ int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t spc,
         return rc;
     int rc = MSK144_OK;
     copy_out(lv, rv, lines, line_cap, nlines, results, result_cap, nresults, &rc);
+    dec->last_lines = std::move(lv);
+    dec->last_results = std::move(rv);
+    return rc;
+}
+
+int msk144_last_output(msk144_decoder* dec, msk144_line* lines, size_t line_cap, size_t* nlines, msk144_result* results,
+                       size_t result_cap, size_t* nresults) {
+    if (!dec) return fail(MSK144_EINVAL, "null argument");
+    int rc = MSK144_OK;
+    copy_out(dec->last_lines, dec->last_results, lines, line_cap, nlines, results, result_cap, nresults, &rc);
     return rc;
 }
 
@@ -746,10 +803,13 @@ int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int
     CK(cudaSetDevice(dec->cfg.device));
     const size_t bytes = spc * static_cast<size_t>(nchan) * 2;  // s16 mono or s8 I + s8 Q: 2 bytes per sample
     if (int rc = dec->ensure_raw(bytes)) return rc;
-    CK(cudaMemcpyAsync(dec->d_raw, samples, bytes, cudaMemcpyHostToDevice, dec->stream));
-    dec->h2d_bytes += bytes;
-    return msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results, result_cap,
-                                nresults);
+    if (int rc = dec->upload_pieces(samples, bytes)) return rc;
+    const int rc = msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results,
+                                        result_cap, nresults);
+    dec->up_pieces = 0;
+    // a call without blocks, or an error, may leave pieces in flight: they must not outlive the caller's buffer
+    cudaStreamSynchronize(dec->up_stream);
+    return rc;
 }
 
 int msk144_deinterleave_device(msk144_decoder* dec, const void* d_in, void* d_out, size_t spc, int nchan, void* stream) {

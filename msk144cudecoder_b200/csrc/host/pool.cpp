@@ -35,6 +35,8 @@ void split(int nchan, int n, std::vector<int>* first, std::vector<int>* count) {
 struct msk144_pool {
     std::vector<msk144_decoder*> dec;
     std::vector<int> device;
+    std::vector<msk144_line> last_lines;      // merged output of the most recent msk144_pool_decode_host
+    std::vector<msk144_result> last_results;
     // streaming: channel ranges fixed by the first push
     int il_nchan = 0;
     std::vector<int> first, count;
@@ -100,21 +102,21 @@ int msk144_pool_decode_host(msk144_pool* p, const void* samples, size_t spc, int
         if (count[i] == 0) return;
         const char* src = static_cast<const char*>(samples) + static_cast<size_t>(first[i]) * spc * 2;
         size_t lcap = 4096, rcap = want_results ? (1u << 16) : 0;
-        for (int attempt = 0; attempt < 2; attempt++) {  // a too small array reports the needed size: one retry
+        pt.lines.resize(lcap);
+        pt.results.resize(rcap);
+        size_t nl = 0, nr = 0;
+        pt.rc = msk144_decode_host(p->dec[i], src, spc, count[i], pt.lines.data(), lcap, &nl,
+                                   rcap ? pt.results.data() : nullptr, rcap, rcap ? &nr : nullptr);
+        if (pt.rc == MSK144_EOVERFLOW) {  // the member keeps its output: fetch it into arrays of the reported sizes
+            lcap = std::max(lcap, nl), rcap = rcap ? std::max(rcap, nr) : 0;
             pt.lines.resize(lcap);
             pt.results.resize(rcap);
-            size_t nl = 0, nr = 0;
-            pt.rc = msk144_decode_host(p->dec[i], src, spc, count[i], pt.lines.data(), lcap, &nl,
-                                       rcap ? pt.results.data() : nullptr, rcap, rcap ? &nr : nullptr);
-            if (pt.rc == MSK144_EOVERFLOW && attempt == 0) {
-                lcap = std::max(lcap, nl), rcap = rcap ? std::max(rcap, nr) : 0;
-                continue;
-            }
-            if (pt.rc != MSK144_OK) pt.err = msk144_last_error();
-            pt.lines.resize(std::min(nl, lcap));
-            pt.results.resize(std::min(nr, rcap));
-            break;
+            pt.rc = msk144_last_output(p->dec[i], pt.lines.data(), lcap, &nl, rcap ? pt.results.data() : nullptr, rcap,
+                                       rcap ? &nr : nullptr);
         }
+        if (pt.rc != MSK144_OK) pt.err = msk144_last_error();
+        pt.lines.resize(std::min(nl, lcap));
+        pt.results.resize(std::min(nr, rcap));
         for (auto& l : pt.lines) l.channel += first[i];
         for (auto& r : pt.results) r.channel += first[i];
     };
@@ -126,17 +128,20 @@ int msk144_pool_decode_host(msk144_pool* p, const void* samples, size_t spc, int
         if (part[i].rc != MSK144_OK) return pfail(part[i].rc, "device " + std::to_string(p->device[i]) + ": " + part[i].err);
     // members hold contiguous channel ranges in order, and each returns its lines channel-major: concatenation
     // is the order a single decoder produces
-    size_t nl = 0, nr = 0;
+    p->last_lines.clear(), p->last_results.clear();
     for (int i = 0; i < n; i++) {
-        for (const auto& l : part[i].lines) {
-            if (lines && nl < line_cap) lines[nl] = l;
-            nl++;
-        }
-        for (const auto& r : part[i].results) {
-            if (results && nr < result_cap) results[nr] = r;
-            nr++;
-        }
+        p->last_lines.insert(p->last_lines.end(), part[i].lines.begin(), part[i].lines.end());
+        p->last_results.insert(p->last_results.end(), part[i].results.begin(), part[i].results.end());
     }
+    return msk144_pool_last_output(p, lines, line_cap, nlines, results, result_cap, nresults);
+}
+
+int msk144_pool_last_output(msk144_pool* p, msk144_line* lines, size_t line_cap, size_t* nlines, msk144_result* results,
+                            size_t result_cap, size_t* nresults) {
+    if (!p) return pfail(MSK144_EINVAL, "null argument");
+    const size_t nl = p->last_lines.size(), nr = p->last_results.size();
+    if (lines) std::memcpy(lines, p->last_lines.data(), std::min(nl, line_cap) * sizeof(msk144_line));
+    if (results) std::memcpy(results, p->last_results.data(), std::min(nr, result_cap) * sizeof(msk144_result));
     if (nlines) *nlines = nl;
     if (nresults) *nresults = nr;
     if ((lines && nl > line_cap) || (results && nr > result_cap)) return pfail(MSK144_EOVERFLOW, "output array too small");

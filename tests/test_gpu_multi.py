@@ -128,3 +128,22 @@ def test_two_ranks_gather_equals_single_gpu(gpu, synth):
     key = lambda ls: sorted(ls, key=lambda t: (t[0], t[1], t[2]))
     assert got[0] == key(strip(single)) and len(got[0]) > 0
     assert set(got[1]) < set(got[0])           # rank 1 keeps only its own share
+
+
+@pytest.mark.gpu
+def test_small_output_arrays_do_not_cost_a_second_decode(gpu, synth):
+    """MSK144_EOVERFLOW reports the sizes needed; msk144_last_output / msk144_pool_last_output then hand over the
+    output the decoder kept -- the kernels run once (kernel_launches of the stage times), and the lines and results
+    are the ones a call with large arrays returns."""
+    x = channels(synth)
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        big, bres = d.decode_host(x, nchan=NCHAN, line_cap=4096, result_cap=1 << 16)
+        launches_one = d.stage_times()["kernel_launches"]
+        small, sres = d.decode_host(x, nchan=NCHAN, line_cap=1, result_cap=1)
+        launches_two = d.stage_times()["kernel_launches"]
+    assert len(big) > 1 and len(bres) > 1
+    assert strip(small) == strip(big) and sres.tobytes() == bres.tobytes()
+    assert launches_two - launches_one == launches_one - 1, (launches_one, launches_two)   # minus the one-off mixer table
+    with gpu.Pool([0, 0], compat_cache=True, **KW) as p:
+        pooled, pres = p.decode_host(x, nchan=NCHAN, line_cap=1, result_cap=1)
+    assert strip(pooled) == strip(big) and pres.tobytes() == bres.tobytes()
