@@ -52,6 +52,10 @@ for step in "$@"; do
         timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $n --steps 3 --warmup 3 --no-cli --no-cpu-baseline > gpurun_out/bench_n$n.log 2> gpurun_out/bench_n$n.err
         echo "bench n=$n rc=$?"; tail -1 gpurun_out/bench_n$n.log | cut -c1-300; tail -3 gpurun_out/bench_n$n.err
       done ;;
+    multi) timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q --timeout=600 > gpurun_out/pytest_multi.log 2>&1; echo "multi rc=$?"; tail -5 gpurun_out/pytest_multi.log
+           timeout 600 python tools/bench_pool.py 128 > gpurun_out/pool_1gpu.jsonl 2> gpurun_out/pool_1gpu.err; cut -c1-330 gpurun_out/pool_1gpu.jsonl; tail -3 gpurun_out/pool_1gpu.err ;;
+    pool8) nvidia-smi -L > gpurun_out/gpus.txt 2>&1
+           timeout 600 python tools/bench_pool.py 256 > gpurun_out/pool_scale.jsonl 2> gpurun_out/pool_scale.err; echo "pool rc=$?"; cut -c1-420 gpurun_out/pool_scale.jsonl; tail -3 gpurun_out/pool_scale.err ;;
     ncu_fft)
       timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
       timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -s 6 -c 40 -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
