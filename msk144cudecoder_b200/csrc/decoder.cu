@@ -14,6 +14,7 @@
 #include <cstring>
 #include <deque>
 #include <memory>
+#include <new>
 #include <string>
 #include <vector>
 
@@ -123,6 +124,27 @@ void launch_scan(int depth, dim3 grid, cudaStream_t st, const ScanParams& sp) {
         scan_entry(depth)<<<grid, SCAN_THREADS, SCAN_SMEM, st>>>(sp);
 }
 
+// Page-locked storage for the streaming input buffers: msk144_push uploads straight from them, so the copy is a DMA
+// from the caller's bytes' first resting place instead of the driver's staging copy of a pageable vector.
+template <class T>
+struct PinnedAlloc {
+    using value_type = T;
+    PinnedAlloc() = default;
+    template <class U>
+    PinnedAlloc(const PinnedAlloc<U>&) {}
+    T* allocate(size_t n) {
+        void* p = nullptr;
+        if (cudaMallocHost(&p, n * sizeof(T)) != cudaSuccess) throw std::bad_alloc();
+        return static_cast<T*>(p);
+    }
+    void deallocate(T* p, size_t) { cudaFreeHost(p); }
+    template <class U>
+    bool operator==(const PinnedAlloc<U>&) const { return true; }
+    template <class U>
+    bool operator!=(const PinnedAlloc<U>&) const { return false; }
+};
+using PinnedBytes = std::vector<uint8_t, PinnedAlloc<uint8_t>>;
+
 struct RawResult {
     int64_t gblock;
     ResultRec r;
@@ -200,12 +222,12 @@ struct msk144_decoder {
     int64_t launches = 0;
 
     // streaming state (msk144_push / msk144_poll)
-    std::vector<uint8_t> pending;  // raw bytes from the start of the next unprocessed block
+    PinnedBytes pending;  // raw bytes from the start of the next unprocessed block (page-locked)
     int share_twins = std::getenv("MSK144_NO_TWINS") ? 0 : 1;  // A/B knob; results are identical either way
     unsigned apmask[4] = {0u, 0u, 0u, 0u};  // MSK144_FLAG_WSJTX_BP: a-priori bits (msk144_set_ap_mask)
     // multi-channel streaming state (msk144_push_interleaved): raw interleaved bytes, one SNR recurrence per channel
     int il_nchan = 0;
-    std::vector<uint8_t> il_pending;
+    PinnedBytes il_pending;
     std::vector<std::unique_ptr<ChanState>> il_state;
     int64_t il_next_block = 0;
     bool wav_checked = false;      // MSK144_FLAG_SKIP_WAV_HEADER: the start of the stream has been examined

@@ -58,8 +58,23 @@ for step in "$@"; do
            timeout 600 python tools/bench_pool.py 256 > gpurun_out/pool_scale.jsonl 2> gpurun_out/pool_scale.err; echo "pool rc=$?"; cut -c1-420 gpurun_out/pool_scale.jsonl; tail -3 gpurun_out/pool_scale.err ;;
     ncu_fft)
       timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
-      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel|rms_kernel' -s 6 -c 40 -f -o gpurun_out/prof_front python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
-      echo "ncu_fft rc=$?"; ls -la gpurun_out/prof_front.ncu-rep ;;
+      # launches of bench_stages.py frontend: (128-block groups) method 2: 3 per run x 7 runs, then method 1: 21, then the 4096-block groups: 2 per run x 7 runs each
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 18 -c 1 -f -o gpurun_out/prof_front_m2_b128 python tools/bench_stages.py frontend > gpurun_out/ncu_front.log 2>&1
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 39 -c 1 -f -o gpurun_out/prof_front_m1_b128 python tools/bench_stages.py frontend >> gpurun_out/ncu_front.log 2>&1
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 52 -c 1 -f -o gpurun_out/prof_front_m2_b4096 python tools/bench_stages.py frontend >> gpurun_out/ncu_front.log 2>&1
+      timeout 600 ncu --set full --clock-control none --import-source on -k regex:'frontend_kernel' -s 66 -c 1 -f -o gpurun_out/prof_front_m1_b4096 python tools/bench_stages.py frontend >> gpurun_out/ncu_front.log 2>&1
+      echo "ncu_fft rc=$?"
+      for r in m2_b128 m1_b128 m2_b4096 m1_b4096; do echo "##### $r"; python tools/ncu_summary.py gpurun_out/prof_front_$r.ncu-rep; done > gpurun_out/ncu_front_summary.txt 2>&1
+      ls -la gpurun_out/prof_front_*.ncu-rep; rm -f gpurun_out/prof_front_*.ncu-rep; head -60 gpurun_out/ncu_front_summary.txt ;;
+    summarize)   # text summaries of gpurun_out/prof_full.ncu-rep on the box (the report itself may be too large to travel)
+      python tools/ncu_summary.py gpurun_out/prof_full.ncu-rep > gpurun_out/ncu_full_summary.txt 2>&1
+      for k in scan_kernel ldpc_kernel; do
+        python tools/ncu_lines.py gpurun_out/prof_full.ncu-rep $k 30 > gpurun_out/ncu_lines_$k.txt 2>&1
+        ncu -i gpurun_out/prof_full.ncu-rep --page source --csv --kernel-name regex:$k > gpurun_out/src_$k.csv 2>/dev/null
+        python tools/sass_hist.py gpurun_out/src_$k.csv 30 > gpurun_out/sass_hist_$k.txt 2>&1; rm -f gpurun_out/src_$k.csv
+      done
+      ncu -i gpurun_out/prof_full.ncu-rep --page raw --csv --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum > gpurun_out/ncu_full_dram.csv 2>&1
+      du -sh gpurun_out ;;
     chz) timeout 900 python -m pytest tests/test_channelizer.py -m gpu -q -s --timeout=600 > gpurun_out/pytest_chz.log 2>&1; echo "chz rc=$?"; grep -E "differ|bin |passed|failed|Error|error" gpurun_out/pytest_chz.log | tail -30
          timeout 600 python tools/bench_channelizer.py > gpurun_out/chz_bench.jsonl 2> gpurun_out/chz_bench.err; cut -c1-500 gpurun_out/chz_bench.jsonl; tail -3 gpurun_out/chz_bench.err ;;
     ncu_chz)
