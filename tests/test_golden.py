@@ -374,3 +374,23 @@ def test_gpu_long_stream_vs_reference(gpu, orc, name):
     assert n_same > 0.9 * len(ref_items) and n_iter <= 0.01 * n_same and n_nbad <= 0.002 * n_same
     # observed: up to 10 flips in a block of ~15,400 gated candidates, 366 over the 4.24 M of the 60 s (8.6e-5)
     assert np.abs(dg).max() <= 16 and np.abs(dg).sum() <= 2e-4 * g["ngated"].sum()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["audio_m2_depth8", "audio_deep", "iq_deep"])
+def test_gpu_second_scan_form_identical(gpu, name):
+    """scan2_kernel (two 448-thread CTAs per SM, MSK144_SCAN_FORM=2; csrc/scan2.cuh) is the same arithmetic in another
+    shape: the CLI under either form prints the same bytes, which are the reference's lines.  The form is chosen once per
+    process, hence the subprocesses."""
+    import subprocess
+    g, raw = load(name)
+    cmd = [gpu.CLI_PATH, f"--search-width={float(g['width'])}", f"--search-step={float(g['step'])}",
+           f"--scan-depth={int(g['depth'])}", f"--nbadsync-threshold={int(g['thr'])}", f"--read-mode={int(g['read_mode'])}",
+           f"--analytic-method={int(g['method'])}", f"--center-frequency={float(g['center'])}"]
+    outs = {}
+    for form in ("1", "2"):
+        p = subprocess.run(cmd, input=raw.tobytes(), capture_output=True, env=dict(os.environ, MSK144_SCAN_FORM=form))
+        assert p.returncode == 0, p.stderr.decode()
+        outs[form] = [re.sub(r"date=\d{14}", "date=" + "x" * 14, l) for l in p.stdout.decode().splitlines()]
+    assert outs["1"] == outs["2"] and len(outs["2"]) > 2
+    assert outs["2"] == [str(s) for s in g["cli_lines"]]
