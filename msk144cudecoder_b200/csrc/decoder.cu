@@ -482,10 +482,15 @@ int msk144_decoder::launch_group(Slot& sl, const void* d_in, long long chan_stri
     lp.flat_out = nullptr;
     std::memcpy(lp.apmask, apmask, sizeof(lp.apmask));
     fill_ldpc_tables(&lp);
+    // MSK144_LDPC_CTAS=1: one persistent LDPC CTA per SM instead of two (experiments with two decoders sharing a GPU)
+    static const int ldpc_ctas = [] {
+        const char* e = std::getenv("MSK144_LDPC_CTAS");
+        return e ? std::max(1, std::min(LDPC_CTAS_PER_SM, std::atoi(e))) : LDPC_CTAS_PER_SM;
+    }();
     if (cfg.flags & MSK144_FLAG_WSJTX_BP)
-        ldpc_kernel<true><<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
+        ldpc_kernel<true><<<sm_count * ldpc_ctas, LDPC_WARPS * 32, 0, st>>>(lp);
     else
-        ldpc_kernel<false><<<sm_count * LDPC_CTAS_PER_SM, LDPC_WARPS * 32, 0, st>>>(lp);
+        ldpc_kernel<false><<<sm_count * ldpc_ctas, LDPC_WARPS * 32, 0, st>>>(lp);
     CK(cudaGetLastError());
     CK(cudaEventRecord(ev[3], st));
     CK(cudaEventRecord(sl.done, st));

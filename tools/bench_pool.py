@@ -38,10 +38,11 @@ def main():
     ngpu = torch.cuda.device_count()
     flags = dict(center=1500.0, width=500.0, step=1.0, depth=6, thr=3)
     base = None
-    for n in (1, 2, 4, 8):
-        if n > ngpu:
-            break
-        with m.Pool(list(range(n)), compat_cache=True, **flags) as p:
+    # optional third argument: an explicit member list such as 0,0 (two decoders sharing GPU 0) instead of the 1/2/4/8 sweep
+    lists = [[int(v) for v in sys.argv[3].split(",")]] if len(sys.argv) > 3 else [list(range(n)) for n in (1, 2, 4, 8) if n <= ngpu]
+    for devs in lists:
+        n = len(devs)
+        with m.Pool(devs, compat_cache=True, **flags) as p:
             p.decode_host(x, nchan=nchan, line_cap=1 << 17)
             t0 = time.perf_counter()
             lines, _ = p.decode_host(x, nchan=nchan, line_cap=1 << 17)
@@ -50,7 +51,8 @@ def main():
                                    for l in lines]).encode()).hexdigest()[:16]
         if base is None:
             base = (dt, key)
-        print(json.dumps({"bench": "cfg5_pool", "n_gpus": n, "channels": nchan, "seconds_per_channel": SECONDS,
+        print(json.dumps({"bench": "cfg5_pool", "n_gpus": len(set(devs)), "members": devs,
+                          "env": {k: os.environ[k] for k in ("MSK144_SCAN_FORM", "MSK144_LDPC_CTAS") if k in os.environ}, "channels": nchan, "seconds_per_channel": SECONDS,
                           "pass_s": dt, "realtime_channels": nchan * SECONDS / dt,
                           "audio_s_per_s": nchan * int(SECONDS * 12000 / 2592 - 1) * 0.216 / dt,
                           "speedup_vs_1": base[0] / dt, "efficiency": base[0] / dt / n, "merged_lines": len(lines),

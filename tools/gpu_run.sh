@@ -56,6 +56,11 @@ for step in "$@"; do
            timeout 600 python tools/bench_pool.py 128 > gpurun_out/pool_1gpu.jsonl 2> gpurun_out/pool_1gpu.err; cut -c1-330 gpurun_out/pool_1gpu.jsonl; tail -3 gpurun_out/pool_1gpu.err ;;
     pool8) nvidia-smi -L > gpurun_out/gpus.txt 2>&1
            timeout 600 python tools/bench_pool.py 256 > gpurun_out/pool_scale.jsonl 2> gpurun_out/pool_scale.err; echo "pool rc=$?"; cut -c1-420 gpurun_out/pool_scale.jsonl; tail -3 gpurun_out/pool_scale.err ;;
+    share)   # two decoders sharing GPU 0: does a scan CTA beside an LDPC CTA on the same SM fill the idle issue slots?
+      run() { env "$@" timeout 300 python tools/bench_pool.py 64 60 "$DEVS" 2>&1 | grep cfg5_pool | cut -c1-330; }
+      DEVS=0 run MSK144_SCAN_FORM=1; DEVS=0 run MSK144_SCAN_FORM=2
+      DEVS=0,0 run MSK144_SCAN_FORM=1; DEVS=0,0 run MSK144_SCAN_FORM=2
+      DEVS=0,0 run MSK144_SCAN_FORM=2 MSK144_LDPC_CTAS=1; DEVS=0,0,0 run MSK144_SCAN_FORM=2 MSK144_LDPC_CTAS=1 ;;
     ncu_fft)
       timeout 300 python tools/bench_stages.py frontend > gpurun_out/stages_frontend.jsonl 2>&1; echo "frontend plain rc=$?"; cut -c1-300 gpurun_out/stages_frontend.jsonl
       # launches of bench_stages.py frontend: (128-block groups) method 2: 3 per run x 7 runs, then method 1: 21, then the 4096-block groups: 2 per run x 7 runs each
