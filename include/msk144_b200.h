@@ -57,10 +57,11 @@ enum {
      * a-priori mask (msk144_set_ap_mask).  Same arithmetic.  Off by default: the drop-in output is the reference's.
      * bpdecode128_90.f90 is not on this box; the mode is restated from the published algorithm (parity unpinned). */
     MSK144_FLAG_WSJTX_BP = 4,
-    /* Host threads waiting for the GPU sleep instead of spinning: msk144_create sets cudaDeviceScheduleBlockingSync on the
-     * decoder's device, as the reference does for its whole process (main.cu:115).  For live use (one 216 ms hop per push,
-     * the GPU busy for a fraction of a millisecond); costs a few tens of microseconds of wake-up latency per poll, so the
-     * batch entry points leave it off.  The CLI sets it. */
+    /* A live receiver's host thread sleeps while it waits for the GPU instead of spinning, as the reference's whole
+     * process does (cudaDeviceScheduleBlockingSync, main.cu:115): the waits of a call that completes at most 8 blocks
+     * (one 216 ms hop completes one) go through a blocking-sync event.  Calls that complete more (a file, a fast pipe)
+     * keep spinning: there a sleeping wait costs throughput (6 % of the CLI's steady-state rate, measured).  The CLI
+     * sets it. */
     MSK144_FLAG_BLOCKING_SYNC = 8
 };
 

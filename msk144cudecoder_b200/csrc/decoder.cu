@@ -207,6 +207,10 @@ struct msk144_decoder {
     std::vector<cudaEvent_t> up_ev;
     size_t up_pieces = 0;  // pieces in flight for the current call (0: input already resident)
     long long up_waited = -1;
+    // MSK144_FLAG_BLOCKING_SYNC: host waits of a live hop sleep on this event instead of spinning (main.cu:115)
+    cudaEvent_t wait_ev = nullptr;
+    bool sleep_wait = false;  // set per decode: the flag is on and the call is a live hop (a few blocks)
+    int host_wait(cudaStream_t s);
     int upload_pieces(const void* h_src, size_t bytes);
     int wait_for_input(size_t end_byte, cudaStream_t st);
     float2* d_twiddle = nullptr;
@@ -289,6 +293,7 @@ void msk144_decoder::release() {
     ev_used = 0;
     if (stream) cudaStreamDestroy(stream), stream = nullptr;
     if (copy_stream) cudaStreamDestroy(copy_stream), copy_stream = nullptr;
+    if (wait_ev) cudaEventDestroy(wait_ev), wait_ev = nullptr;
     for (auto& e : up_ev) cudaEventDestroy(e);
     up_ev.clear();
     if (up_stream) cudaStreamDestroy(up_stream), up_stream = nullptr;
@@ -325,6 +330,16 @@ int msk144_decoder::ensure_raw(size_t bytes) {
     d_raw = nullptr, d_raw_bytes = 0;
     CK(cudaMalloc(&d_raw, bytes));
     d_raw_bytes = bytes;
+    return 0;
+}
+
+int msk144_decoder::host_wait(cudaStream_t s) {
+    if (sleep_wait && wait_ev) {
+        CK(cudaEventRecord(wait_ev, s));
+        CK(cudaEventSynchronize(wait_ev));
+    } else {
+        CK(cudaStreamSynchronize(s));
+    }
     return 0;
 }
 
@@ -504,7 +519,7 @@ int msk144_decoder::fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, i
     CK(cudaStreamWaitEvent(cs, sl.done, 0));
     CK(cudaMemcpyAsync(sl.h_counters, sl.d_counters, 4 * sizeof(int), cudaMemcpyDeviceToHost, cs));
     CK(cudaMemcpyAsync(sl.h_powers, sl.d_powers, static_cast<size_t>(nb) * 8 * sizeof(float), cudaMemcpyDeviceToHost, cs));
-    CK(cudaStreamSynchronize(cs));
+    if (int rc = host_wait(cs)) return rc;
     const int qn = sl.h_counters[0], rn = sl.h_counters[1];
     if (static_cast<size_t>(qn) > queue_cap || static_cast<size_t>(rn) > result_cap)
         return fail(MSK144_EOVERFLOW, "device queue overflow");
@@ -515,7 +530,7 @@ int msk144_decoder::fetch_group(Slot& sl, int nb, std::vector<RawResult>* out, i
     if (rn > 0) {
         if (int rc = ensure_host_results(rn)) return rc;
         CK(cudaMemcpyAsync(h_results, sl.d_results, static_cast<size_t>(rn) * sizeof(ResultRec), cudaMemcpyDeviceToHost, cs));
-        CK(cudaStreamSynchronize(cs));
+        if (int rc = host_wait(cs)) return rc;
         d2h_bytes += static_cast<size_t>(rn) * sizeof(ResultRec);
         if (out)
             for (int i = 0; i < rn; i++) out->push_back(RawResult{gblock0 + h_results[i].block, h_results[i]});
@@ -534,6 +549,9 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
     if (bpc > 0x7fffffff) return fail(MSK144_EINVAL, "channel too long for one call");
     const int group = std::max(1, cfg.max_batch_blocks);
     if (int rc = ensure_capacity(static_cast<int>(std::min<int64_t>(group, total)))) return rc;
+    // a live receiver completes one block per 216 ms hop: its waits sleep; a file or a fast pipe completes a launch
+    // group per call, where a sleeping wait would cost throughput (measured: 6 % of the CLI's steady-state rate)
+    sleep_wait = (cfg.flags & MSK144_FLAG_BLOCKING_SYNC) != 0 && total <= 8;
     std::vector<RawResult> raw;
     std::vector<float> powers;
     const bool compat = (cfg.flags & MSK144_FLAG_COMPAT_DECODE_CACHE) != 0;
@@ -627,7 +645,7 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
     }
     if (int rc = fetch_group(slot[cur ^ 1], prev_nb, &raw, prev_g0, &powers)) return rc;
     process(prev_g0, prev_nb);
-    CK(cudaStreamSynchronize(st));
+    if (int rc = host_wait(st)) return rc;
     collect_times();
     times.kernel_launches = launches;
     return 0;
@@ -666,10 +684,6 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
         return fail(MSK144_ENODEV, "no CUDA device: this library has no CPU path");
     if (cfg->device < 0 || cfg->device >= ndev) return fail(MSK144_EINVAL, "bad device ordinal");
     CK(cudaSetDevice(cfg->device));
-    if (cfg->flags & MSK144_FLAG_BLOCKING_SYNC) {
-        // main.cu:115.  A device whose context another part of the process already configured keeps its setting.
-        if (cudaSetDeviceFlags(cudaDeviceScheduleBlockingSync) != cudaSuccess) cudaGetLastError();
-    }
     cudaDeviceProp prop;
     CK(cudaGetDeviceProperties(&prop, cfg->device));
     if (prop.major < 10)
@@ -722,6 +736,7 @@ int msk144_create(const msk144_config* cfg, msk144_decoder** out) {
         d->launches += 1;
     }
     CKD(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+    if (cfg->flags & MSK144_FLAG_BLOCKING_SYNC) CKD(cudaEventCreateWithFlags(&d->wait_ev, cudaEventBlockingSync | cudaEventDisableTiming));
     for (auto& sl : d->slot) {
         CKD(cudaMalloc(&sl.d_counters, 4 * sizeof(int)));
         CKD(cudaMallocHost(&sl.h_counters, 4 * sizeof(int)));
