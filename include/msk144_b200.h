@@ -336,6 +336,35 @@ int msk144_channelize_host(msk144_channelizer* chz, const void* in, size_t nbyte
 int msk144_channelizer_push(msk144_channelizer* chz, const void* bytes, size_t nbytes, int8_t* out, size_t out_cap_frames, size_t* nframes);
 int msk144_channelizer_reset(msk144_channelizer* chz);
 
+/* ---- front end without any allocation --------------------------------------------------------------------------
+ * No counterpart in the reference (a stand-alone process that allocates its block buffers itself: main.cu:214-216).
+ * For code that holds device buffers but is not allowed to allocate at the point where it wants the front end run:
+ * a plugin running inside a host application that owns the whole memory budget (a torch caching allocator, an SDR
+ * framework's arena), a real-time receive loop in which cudaMalloc / cudaFree would stall every stream of the device
+ * (both synchronise it), or a process that has deliberately handed all free HBM to something else.  Every other entry
+ * point of this library needs a decoder, and msk144_create allocates.  This one needs none.
+ *
+ * It runs the method-2 front end (--analytic-method=2 for s16 audio, the IQ low-pass for --read-mode=2) of ONE channel:
+ * d_samples[nsamples] -> d_blocks_re_im[nblocks][5184][2] and d_powers8[nblocks][8], nblocks = (nsamples - 5184) / 2592 + 1
+ * (0 if nsamples < 5184); the same kernels and the same bits as msk144_frontend_host.  All three pointers are DEVICE
+ * memory of the CURRENT device (cudaSetDevice is the caller's), supplied and sized by the caller; `stream` is a
+ * cudaStream_t (NULL = the default stream); the call is asynchronous and returns once the kernels are queued.
+ *
+ * The one thing the pipeline allocates for this stage, 1 / rms per block between its two kernels, lives in a fixed
+ * array inside the library's device image instead: 4 bytes x MSK144_NOALLOC_MAX_BLOCKS = 32 KB on every GPU that
+ * loads the library, held until the process exits.  Consequences:
+ *   - a call with more than MSK144_NOALLOC_MAX_BLOCKS blocks (nsamples > 2592 x 8193) is refused with MSK144_EINVAL;
+ *     cut longer input into pieces that overlap by 2592 samples;
+ *   - every call on a GPU uses the same array.  Calls that follow each other on one stream are fine (each call
+ *     rewrites every entry it reads; nothing is carried over and nothing needs clearing), but two calls that can run
+ *     on the GPU at the same time (different streams, different host threads) race on it and must be serialised by the caller;
+ *   - the first call on each device looks up the array's device address and raises the kernel's shared-memory limit;
+ *     make that first call before starting any stream capture on that device.
+ * No cudaMalloc, cudaFree, cudaMallocHost or other allocating routine is called, on any path. */
+#define MSK144_NOALLOC_MAX_BLOCKS 8192
+int msk144_frontend_device_noalloc(const void* d_samples, size_t nsamples, int read_mode, float* d_blocks_re_im,
+                                   float* d_powers8, void* stream, int64_t* nblocks_out);
+
 /* ---- measurement helpers -------------------------------------------------------------------------------------- */
 /* Sustained FP32 FMA rate of the decoder's device: a dependency-free FFMA stream (8 independent chains per thread,
  * every SM sub-partition saturated), timed with CUDA events; *tflops = 2 * FMAs / time.  This is the measured

@@ -40,7 +40,9 @@ EXPORTED_SYMBOLS = [
     "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math", "msk144_set_ap_mask",
     "msk144_channelizer_create", "msk144_channelizer_destroy", "msk144_channelizer_prototype", "msk144_channelizer_launches",
     "msk144_channelize_device", "msk144_channelize_host", "msk144_channelizer_push", "msk144_channelizer_reset",
+    "msk144_frontend_device_noalloc",
 ]
+NOALLOC_MAX_BLOCKS = 8192  # MSK144_NOALLOC_MAX_BLOCKS
 IQ_U8, IQ_S8, IQ_S16 = 1, 2, 3
 
 
@@ -129,6 +131,7 @@ def lib():
         L.msk144_deinterleave_device.argtypes = [vp, vp, vp, sz, C.c_int, vp]
         L.msk144_run_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(C.c_int64)]
         L.msk144_frontend_host.argtypes = [vp, vp, sz, vp, vp, C.POINTER(C.c_int64)]
+        L.msk144_frontend_device_noalloc.argtypes = [vp, sz, C.c_int, vp, vp, vp, C.POINTER(C.c_int64)]
         L.msk144_scan_host.argtypes = [vp, vp, C.c_int64, vp, vp, vp, sz, C.POINTER(sz)]
         L.msk144_ldpc_decode_host.argtypes = [vp, vp, sz, vp, vp, vp, vp]
         L.msk144_ldpc_decode_device.argtypes = [vp, vp, sz, vp, vp]
@@ -530,6 +533,17 @@ def do_decode(ctx: MSK144SearchContext, samples: np.ndarray, nchan: int = 1):
     """main.cu:428-532 for every block of `samples` (raw stdin samples, not a pre-filtered block: the
     front end runs on the GPU too).  Returns (lines, results)."""
     return ctx.decode_host(samples, nchan)
+
+
+def frontend_device_noalloc(d_samples: int, nsamples: int, read_mode: int, d_blocks: int, d_powers: int,
+                            stream: int = 0) -> int:
+    """msk144_frontend_device_noalloc: the method-2 / IQ front end over device buffers the caller already owns, for
+    callers that may not allocate (see include/msk144_b200.h).  All pointers are device addresses on the current CUDA
+    device; asynchronous on `stream`.  Returns the number of blocks written.  At most NOALLOC_MAX_BLOCKS blocks per
+    call; calls that can overlap on the GPU share one scratch array and must be serialised by the caller."""
+    n = C.c_int64(0)
+    _check(lib().msk144_frontend_device_noalloc(d_samples, nsamples, read_mode, d_blocks, d_powers, stream, C.byref(n)))
+    return n.value
 
 
 def decode_message(bits77: np.ndarray) -> Optional[str]:

@@ -7,6 +7,7 @@
 #include "../../include/msk144_b200.h"
 
 #include <algorithm>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdio>
@@ -14,6 +15,7 @@
 #include <cstring>
 #include <deque>
 #include <memory>
+#include <mutex>
 #include <new>
 #include <string>
 #include <vector>
@@ -1280,3 +1282,104 @@ int msk144_format_line(const msk144_line* line, const char* date14, char* out, s
 }
 
 }  // extern "C"
+
+// =====================================================================================================
+// msk144_frontend_device_noalloc: the method-2 / IQ front end for callers that must not allocate.
+//
+// The pipeline's front end keeps 1 / rms of every block in a cudaMalloc'ed array between rms_kernel and
+// frontend_kernel (Slot::d_fac).  Here that array is the file-scope device array below, which the CUDA module of
+// this library carries on every GPU that loads it: 32 KB per GPU, from the first use of the library on that GPU
+// until the process exits.  Nothing in this section calls cudaMalloc / cudaFree / cudaMallocHost or any other
+// allocating routine, and the success path does not touch the host heap either.
+// =====================================================================================================
+static __device__ __align__(256) float g_noalloc_fac[MSK144_NOALLOC_MAX_BLOCKS];
+
+namespace {
+
+// In host code `g_noalloc_fac` is only the host-side handle of the symbol, not a device address: a kernel handed
+// that name would read host memory or fault.  The device address differs from GPU to GPU, so it is looked up
+// once per device, with that device current, and kept here.
+constexpr int NOALLOC_MAX_DEVICES = 64;
+struct NoAllocDevice {
+    std::atomic<int> ready{0};
+    float* fac = nullptr;
+};
+NoAllocDevice g_noalloc_dev[NOALLOC_MAX_DEVICES];
+std::mutex g_noalloc_mutex;
+
+// Set-up for the CURRENT device (ordinal `dev`): device address of the scratch array, and the opt-in for the
+// 82 KB of dynamic shared memory frontend_kernel needs (per device, so it cannot lean on msk144_create having
+// run on some other GPU).  Neither call allocates.
+int noalloc_setup(int dev, float** fac) {
+    NoAllocDevice& d = g_noalloc_dev[dev];
+    if (d.ready.load(std::memory_order_acquire)) {
+        *fac = d.fac;
+        return MSK144_OK;
+    }
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!d.ready.load(std::memory_order_relaxed)) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_noalloc_fac));
+        if (!p) return fail(MSK144_ECUDA, "cudaGetSymbolAddress returned no address for the scratch array");
+        CK(cudaFuncSetAttribute(frontend_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(FRONT_SMEM)));
+        d.fac = static_cast<float*>(p);
+        d.ready.store(1, std::memory_order_release);
+    }
+    *fac = d.fac;
+    return MSK144_OK;
+}
+
+}  // namespace
+
+extern "C" int msk144_frontend_device_noalloc(const void* d_samples, size_t nsamples, int read_mode, float* d_blocks_re_im,
+                                              float* d_powers8, void* stream, int64_t* nblocks_out) {
+    if (nblocks_out) *nblocks_out = 0;
+    if (!d_samples || !d_blocks_re_im || !d_powers8) return fail(MSK144_EINVAL, "null device pointer");
+    if (read_mode != 1 && read_mode != 2) return fail(MSK144_EINVAL, "read_mode must be 1 (s16 audio) or 2 (s8 I/Q pairs)");
+    if ((reinterpret_cast<uintptr_t>(d_blocks_re_im) & 7) || (reinterpret_cast<uintptr_t>(d_powers8) & 3) ||
+        (read_mode == 1 && (reinterpret_cast<uintptr_t>(d_samples) & 1)))
+        return fail(MSK144_EINVAL, "misaligned device pointer (blocks: 8 bytes, powers: 4, s16 samples: 2)");
+    const int64_t total = nsamples >= static_cast<size_t>(N) ? static_cast<int64_t>((nsamples - N) / (N / 2)) + 1 : 0;
+    if (total > MSK144_NOALLOC_MAX_BLOCKS) {
+        char msg[192];
+        std::snprintf(msg, sizeof(msg),
+                      "%lld blocks in one call, but the static scratch of msk144_frontend_device_noalloc holds %d: pass at most %lld samples per call",
+                      static_cast<long long>(total), MSK144_NOALLOC_MAX_BLOCKS,
+                      static_cast<long long>(MSK144_NOALLOC_MAX_BLOCKS + 1) * (N / 2));
+        return fail(MSK144_EINVAL, msg);
+    }
+    if (nblocks_out) *nblocks_out = total;
+    if (total == 0) return MSK144_OK;
+    int dev = -1;
+    CK(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) return fail(MSK144_EINVAL, "device ordinal beyond the per-device table (64)");
+    float* fac = nullptr;
+    if (int rc = noalloc_setup(dev, &fac)) return rc;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int nb = static_cast<int>(total);
+    if (read_mode == 1) {
+        // every entry frontend_kernel reads below is written here first, so what an earlier call left in the array
+        // never shows; nothing in it has to start at zero
+        RmsParams rp;
+        rp.raw = static_cast<const short*>(d_samples);
+        rp.chan_stride = static_cast<long long>(nsamples);
+        rp.bpc = nb;
+        rp.block0 = 0;
+        rp.nblocks = nb;
+        rp.fac = fac;
+        rms_kernel<<<(nb + 31) / 32, 32, 0, st>>>(rp);
+        CK(cudaGetLastError());
+    }
+    FrontParams fp;
+    fp.raw = d_samples;
+    fp.chan_stride = static_cast<long long>(nsamples);
+    fp.bpc = nb;
+    fp.read_mode = read_mode;
+    fp.block0 = 0;
+    fp.out = reinterpret_cast<float2*>(d_blocks_re_im);
+    fp.powers = d_powers8;
+    fp.fac = read_mode == 1 ? fac : nullptr;  // the IQ path has no rms step (main.cu:365-371) and uses no scratch
+    frontend_kernel<<<nb, FRONT_THREADS, FRONT_SMEM, st>>>(fp);
+    CK(cudaGetLastError());
+    return MSK144_OK;
+}
