@@ -267,11 +267,19 @@ int main(int argc, char* const argv[]) {
             std::cerr << "Warning: Working loop takes too much time: " << ms << " ms"
                       << " of " << 210.0 * blocks_in << " ms max." << std::endl;
     }
-    if (rc_exit != 0) {  // error: the reader may sit in read() for ever; leave without joining it
+    bool reader_finished;
+    {
+        std::lock_guard<std::mutex> lk(inbox.m);
+        reader_finished = inbox.eof;
+    }
+    if (rc_exit != 0 && !reader_finished) {
+        // a push failed while input is still arriving: the reader may sit in read() for ever; leave without joining it
         std::cout.flush();
         std::cerr.flush();
         _exit(rc_exit);
     }
+    // end of input, or a read() error (the reader has returned in both cases): the reference ends its loop on the short
+    // read and prints its epilogue, and so does this; the exit code still reports the error
     reader.join();
     // main.cu:274-278,289-293: the final short fread ends the loop
     size_t leftover;

@@ -17,6 +17,7 @@
 #include <memory>
 #include <mutex>
 #include <new>
+#include <stdexcept>
 #include <string>
 #include <vector>
 
@@ -146,6 +147,24 @@ struct PinnedAlloc {
     bool operator!=(const PinnedAlloc<U>&) const { return false; }
 };
 using PinnedBytes = std::vector<uint8_t, PinnedAlloc<uint8_t>>;
+
+// Append to a streaming input buffer.  The buffer is drained to less than one block after every push, so growing it
+// to exactly what this push needs (rounded up to 64 KB) instead of letting the vector double keeps the page-locked
+// allocation at the size of the largest push seen, and reallocation (a cudaMallocHost plus a synchronising
+// cudaFreeHost) stops after the first few pushes.  PinnedAlloc reports failure by throwing; nothing may throw across
+// the C ABI, so it ends here.
+int append_pinned(PinnedBytes* v, const uint8_t* b, size_t nbytes) {
+    try {
+        const size_t need = v->size() + nbytes;
+        if (need > v->capacity()) v->reserve((need + 65535) / 65536 * 65536);
+        v->insert(v->end(), b, b + nbytes);
+    } catch (const std::bad_alloc&) {
+        return fail(MSK144_ENOMEM, "page-locked input buffer: cudaMallocHost failed");
+    } catch (const std::length_error&) {
+        return fail(MSK144_ENOMEM, "input buffer larger than the address space");
+    }
+    return MSK144_OK;
+}
 
 struct RawResult {
     int64_t gblock;
@@ -847,12 +866,19 @@ int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int
     CK(cudaSetDevice(dec->cfg.device));
     const size_t bytes = spc * static_cast<size_t>(nchan) * 2;  // s16 mono or s8 I + s8 Q: 2 bytes per sample
     if (int rc = dec->ensure_raw(bytes)) return rc;
-    if (int rc = dec->upload_pieces(samples, bytes)) return rc;
-    const int rc = msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results,
-                                        result_cap, nresults);
+    // one exit path: a call without blocks, or an error (in the upload itself included), may leave pieces in flight;
+    // they must not outlive the caller's buffer, and a stale piece count must not make the next call wait on events
+    // of this one
+    int rc = dec->upload_pieces(samples, bytes);
+    std::string upload_err;
+    if (rc != MSK144_OK)
+        upload_err = g_err;
+    else
+        rc = msk144_decode_device(dec, dec->d_raw, spc, nchan, dec->stream, lines, line_cap, nlines, results, result_cap,
+                                  nresults);
     dec->up_pieces = 0;
-    // a call without blocks, or an error, may leave pieces in flight: they must not outlive the caller's buffer
-    cudaStreamSynchronize(dec->up_stream);
+    if (dec->up_stream) cudaStreamSynchronize(dec->up_stream);
+    if (!upload_err.empty()) return fail(rc, upload_err);
     return rc;
 }
 
@@ -927,7 +953,7 @@ int msk144_push(msk144_decoder* dec, const void* bytes, size_t nbytes) {
     if (!dec || (!bytes && nbytes)) return fail(MSK144_EINVAL, "bad argument");
     CK(cudaSetDevice(dec->cfg.device));
     const uint8_t* b = static_cast<const uint8_t*>(bytes);
-    dec->pending.insert(dec->pending.end(), b, b + nbytes);
+    if (int rc = append_pinned(&dec->pending, b, nbytes)) return rc;
     if ((dec->cfg.flags & MSK144_FLAG_SKIP_WAV_HEADER) && !dec->wav_checked) {
         // start of the stream: recognise a RIFF/WAVE header and drop it (adapters.cpp)
         const int64_t off = msk144_wav_data_offset(dec->pending.data(), dec->pending.size(), nullptr, nullptr, nullptr);
@@ -965,7 +991,7 @@ int msk144_push_interleaved(msk144_decoder* dec, const void* bytes, size_t nbyte
     }
     CK(cudaSetDevice(dec->cfg.device));
     const uint8_t* b = static_cast<const uint8_t*>(bytes);
-    dec->il_pending.insert(dec->il_pending.end(), b, b + nbytes);
+    if (int rc = append_pinned(&dec->il_pending, b, nbytes)) return rc;
     const size_t frame = 2 * static_cast<size_t>(nchan);  // one time step of every channel
     const size_t nsteps = dec->il_pending.size() / frame;
     if (nsteps < static_cast<size_t>(N)) return MSK144_OK;

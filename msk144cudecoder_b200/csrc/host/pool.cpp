@@ -42,6 +42,10 @@ struct msk144_pool {
     std::vector<int> first, count;
     std::vector<msk144_line> out_lines;
     size_t out_head = 0;
+    // a member failed in mid-stream: the members are no longer at the same block, so every further push is refused
+    // until msk144_pool_reset_stream (lines already produced stay pollable)
+    bool stream_failed = false;
+    std::string stream_error;
 };
 
 extern "C" {
@@ -150,6 +154,8 @@ int msk144_pool_last_output(msk144_pool* p, msk144_line* lines, size_t line_cap,
 
 int msk144_pool_push_interleaved(msk144_pool* p, const void* bytes, size_t nbytes, int nchan) {
     if (!p || (!bytes && nbytes) || nchan < 1) return pfail(MSK144_EINVAL, "bad argument");
+    if (p->stream_failed)
+        return pfail(MSK144_EINVAL, "an earlier push failed (" + p->stream_error + "): msk144_pool_reset_stream before pushing again");
     const int n = static_cast<int>(p->dec.size());
     if (p->il_nchan == 0) {
         p->il_nchan = nchan;
@@ -176,16 +182,22 @@ int msk144_pool_push_interleaved(msk144_pool* p, const void* bytes, size_t nbyte
         pt.sub.resize(steps * sub_frame);
         const unsigned char* src = static_cast<const unsigned char*>(bytes) + 2 * static_cast<size_t>(c0);
         for (size_t t = 0; t < steps; t++) std::memcpy(pt.sub.data() + t * sub_frame, src + t * frame, sub_frame);
-        pt.rc = cn == 1 ? msk144_push(p->dec[i], pt.sub.data(), pt.sub.size())
-                        : msk144_push_interleaved(p->dec[i], pt.sub.data(), pt.sub.size(), cn);
+        // the interleaved form for a single channel too: it is what ONE decoder would run for this column, and unlike
+        // msk144_push it never looks at MSK144_FLAG_SKIP_WAV_HEADER (a multi-channel stream has no RIFF header)
+        pt.rc = msk144_push_interleaved(p->dec[i], pt.sub.data(), pt.sub.size(), cn);
         if (pt.rc != MSK144_OK) {
             pt.err = msk144_last_error();
             return;
         }
         std::vector<msk144_line> buf(1024);
-        size_t got = 0;
+        size_t got;
         do {
-            msk144_poll(p->dec[i], buf.data(), buf.size(), &got);
+            got = 0;
+            const int prc = msk144_poll(p->dec[i], buf.data(), buf.size(), &got);
+            if (prc != MSK144_OK) {
+                pt.rc = prc, pt.err = msk144_last_error();
+                return;
+            }
             for (size_t k = 0; k < got; k++) {
                 buf[k].channel += c0;
                 pt.lines.push_back(buf[k]);
@@ -196,16 +208,22 @@ int msk144_pool_push_interleaved(msk144_pool* p, const void* bytes, size_t nbyte
     for (int i = 1; i < n; i++) th.emplace_back(work, i);
     work(0);
     for (auto& t : th) t.join();
-    for (int i = 0; i < n; i++)
-        if (part[i].rc != MSK144_OK) return pfail(part[i].rc, "device " + std::to_string(p->device[i]) + ": " + part[i].err);
     // members hold contiguous channel ranges in order; (block, channel) order is what one decoder's
-    // msk144_push_interleaved emits, independent of how the pushes were chunked
+    // msk144_push_interleaved emits, independent of how the pushes were chunked.  If a member failed, the lines the
+    // others produced from this push are still delivered (they have consumed their columns and will not produce them
+    // again), and the stream is marked failed.
     std::vector<msk144_line> merged;
     for (int i = 0; i < n; i++) merged.insert(merged.end(), part[i].lines.begin(), part[i].lines.end());
     std::stable_sort(merged.begin(), merged.end(), [](const msk144_line& a, const msk144_line& b) {
         return a.block_index != b.block_index ? a.block_index < b.block_index : a.channel < b.channel;
     });
     p->out_lines.insert(p->out_lines.end(), merged.begin(), merged.end());
+    for (int i = 0; i < n; i++)
+        if (part[i].rc != MSK144_OK) {
+            p->stream_failed = true;
+            p->stream_error = "device " + std::to_string(p->device[i]) + ": " + part[i].err;
+            return pfail(part[i].rc, p->stream_error);
+        }
     return MSK144_OK;
 }
 
@@ -222,6 +240,7 @@ int msk144_pool_reset_stream(msk144_pool* p) {
     if (!p) return pfail(MSK144_EINVAL, "null argument");
     for (auto* d : p->dec) msk144_reset_stream(d);
     p->il_nchan = 0, p->first.clear(), p->count.clear(), p->out_lines.clear(), p->out_head = 0;
+    p->stream_failed = false, p->stream_error.clear();
     return MSK144_OK;
 }
 

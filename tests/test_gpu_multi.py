@@ -69,6 +69,56 @@ def test_pool_streaming_equals_single_decoder(gpu, synth):
 
 
 @pytest.mark.gpu
+@pytest.mark.parametrize("members,flags", [(NCHAN, 0), (NCHAN + 2, 0), (NCHAN, 2)])
+def test_pool_streaming_one_channel_per_member(gpu, synth, members, flags):
+    """As many members as channels (and more: the extra ones own nothing): every member streams ONE column.  It runs
+    the interleaved form like the single decoder does, so MSK144_FLAG_SKIP_WAV_HEADER (flags=2, which only the
+    one-channel msk144_push honours) changes nothing."""
+    x = channels(synth)
+    raw = np.ascontiguousarray(x.T).tobytes()
+    hop = 2592 * 2 * NCHAN
+    with gpu.Decoder(compat_cache=True, flags=flags, **KW) as d:
+        single = []
+        for off in range(0, len(raw), 3 * hop):
+            d.push(raw[off:off + 3 * hop], nchan=NCHAN)
+            single += d.poll()
+    with gpu.Pool([0] * members, compat_cache=True, flags=flags, **KW) as p:
+        pooled = []
+        for off in range(0, len(raw), 2 * hop):     # chunked differently from the single decoder on purpose
+            p.push(raw[off:off + 2 * hop], NCHAN)
+            pooled += p.poll()
+    assert len(single) > 0 and strip(pooled) == strip(single)
+
+
+@pytest.mark.gpu
+def test_pool_streaming_member_failure_keeps_lines_and_asks_for_reset(gpu, synth):
+    """One member fails in mid-stream: the push reports it, the lines the other members produced from that push are
+    still delivered, further pushes are refused until msk144_pool_reset_stream, and after the reset the pool works."""
+    import ctypes as C
+    x = channels(synth)
+    raw = np.ascontiguousarray(x.T).tobytes()
+    frame = 2 * NCHAN
+    L = gpu.lib()
+    with gpu.Pool([0, 0], compat_cache=True, **KW) as p:
+        p.push(raw, NCHAN)
+        healthy = p.poll()
+        assert len(healthy) > 0
+        p.reset_stream()
+        # member 1 (channels 3, 4) is put out of step behind the pool's back: its stream now expects 3 channels
+        m1 = L.msk144_pool_member(p._h, 1)
+        assert m1 and L.msk144_push_interleaved(m1, None, 0, 3) == 0
+        with pytest.raises(gpu.Msk144Error, match="device 0: channel count changed"):
+            p.push(raw, NCHAN)
+        kept = p.poll()                              # member 0's lines of the failed push
+        assert strip(kept) == strip([l for l in healthy if l["channel"] < 3]) and len(kept) > 0
+        with pytest.raises(gpu.Msk144Error, match="earlier push failed"):
+            p.push(raw[:frame], NCHAN)
+        p.reset_stream()
+        p.push(raw, NCHAN)
+        assert strip(p.poll()) == strip(healthy)
+
+
+@pytest.mark.gpu
 def test_cli_devices_equals_single_device(gpu, synth):
     import subprocess
     x = channels(synth)

@@ -215,6 +215,19 @@ def test_empty_and_short_inputs(gpu):
         assert lines == [] and len(res) == 0
 
 
+def test_cli_read_error_prints_epilogue_and_exit_code(gpu):
+    """A failing read() ends the loop like the reference's short fread does (main.cu:274-278): the epilogue is printed
+    and the decoder destroyed; the exit code reports the error.  stdin = a directory makes read() fail with EISDIR."""
+    fd = os.open("/", os.O_RDONLY)
+    try:
+        r = subprocess.run([gpu.CLI_PATH, "--search-width=100", "--scan-depth=3"], stdin=fd, capture_output=True, timeout=120)
+    finally:
+        os.close(fd)
+    assert r.returncode == 2
+    assert b"read: Is a directory" in r.stderr and b"Incomplete read error. rc=0" in r.stderr
+    assert r.stdout.decode().splitlines()[-1] == "Done"
+
+
 def test_cli_wav_json_dedupe(gpu, synth):
     """Extensions either side of the path: a RIFF header is skipped with --wav (and decoded as 22 samples
     without it, as the reference does); --json carries the same fields; --dedupe prints one line per ping."""
