@@ -186,6 +186,28 @@ int msk144_decode_device(msk144_decoder* dec, const void* d_samples, size_t samp
 int msk144_last_output(msk144_decoder* dec, msk144_line* lines, size_t line_cap, size_t* nlines,
                        msk144_result* results, size_t result_cap, size_t* nresults);
 
+/* ---- ONE channel split in time (SURVEY.md section 8e "Partitioning"; no counterpart in the reference, which is one
+ * process on one GPU).  The only things that cross blocks are on the host: the SNR recurrence (snr_tracker.cu:39-50,
+ * fed by 8 sub-block powers per block) and the call-sign hash tables of the text decoder; on the device a block needs
+ * nothing but its own 5184 samples, and consecutive blocks overlap by half (main.cu:284-288).  So a long stream is cut
+ * into pieces of consecutive blocks, each piece runs the GPU stages on any decoder (any GPU, any process), and ONE
+ * ordered host pass over the pieces' output prints exactly the lines of an undivided decode.
+ * `_chunk_host`: the piece that starts at block `block_base` of its channel: samples[nsamples] begins at sample
+ * 2592 x block_base of the channel and holds nb = (nsamples - 5184) / 2592 + 1 blocks (the piece of blocks [b0, b1) is
+ * samples [2592 b0, 2592 (b1 - 1) + 5184)).  Returns every LDPC success (block_index = block_base + k, channel 0, in
+ * (block, item) order) and powers8[nb][8]; no SNR, no text.  MSK144_EOVERFLOW: fetch with msk144_last_output. */
+int msk144_decode_chunk_host(msk144_decoder* dec, const void* samples, size_t nsamples, int64_t block_base,
+                             msk144_result* results, size_t result_cap, size_t* nresults, float* powers8,
+                             size_t power_cap_blocks, int64_t* nblocks_out);
+/* `_replay_channel`: main.cu:388-419 for blocks [first_block, first_block + nblocks) of one channel, from the start of
+ * the channel's state: SNR recurrence over powers8[nblocks][8], then per block the i3/n3 gate, unpack77 (hash tables in
+ * stream order) and ResultFilter over that block's results.  `results` = the pieces' results concatenated in block
+ * order.  Host only, no GPU.  flags: MSK144_FLAG_COMPAT_DECODE_CACHE as for msk144_create; `channel` is copied into
+ * the lines.  MSK144_EOVERFLOW: *nlines is the size needed, call again (the pass is cheap). */
+int msk144_replay_channel(int32_t flags, int32_t channel, int64_t first_block, int64_t nblocks, const float* powers8,
+                          const msk144_result* results, size_t nresults, msk144_line* lines, size_t line_cap,
+                          size_t* nlines);
+
 /* Multi-channel input as a channeliser / multi-receiver front end delivers it: one sample of every channel per time
  * step (samples[t][c], 2 bytes each).  The reference reads one channel from stdin (main.cu:261-298); this is the ingest
  * adapter of SURVEY.md section 8f.  `_device`: transposes d_in [spc][nchan] into d_out [nchan][spc] (the layout of
@@ -284,7 +306,9 @@ int msk144_pool_create(const msk144_config* cfg, const int32_t* devices, int32_t
 void msk144_pool_destroy(msk144_pool* pool);
 int msk144_pool_size(const msk144_pool* pool);
 msk144_decoder* msk144_pool_member(msk144_pool* pool, int32_t i); /* for msk144_get_stage_times etc. */
-/* == msk144_decode_host over all members */
+/* == msk144_decode_host over all members.  With fewer channels than members the channels are ALSO split in time: each
+ * channel gets a balanced share of the members, every one of them runs msk144_decode_chunk_host on a contiguous range
+ * of the channel's blocks, and the pool runs msk144_replay_channel once per channel; same lines, same order. */
 int msk144_pool_decode_host(msk144_pool* pool, const void* samples, size_t samples_per_channel, int nchan,
                             msk144_line* lines, size_t line_cap, size_t* nlines,
                             msk144_result* results, size_t result_cap, size_t* nresults);

@@ -40,7 +40,7 @@ EXPORTED_SYMBOLS = [
     "msk144_measure_fp32_peak", "msk144_build_info", "msk144_selftest_ldpc_math", "msk144_set_ap_mask",
     "msk144_channelizer_create", "msk144_channelizer_destroy", "msk144_channelizer_prototype", "msk144_channelizer_launches",
     "msk144_channelize_device", "msk144_channelize_host", "msk144_channelizer_push", "msk144_channelizer_reset",
-    "msk144_frontend_device_noalloc",
+    "msk144_frontend_device_noalloc", "msk144_decode_chunk_host", "msk144_replay_channel",
 ]
 NOALLOC_MAX_BLOCKS = 8192  # MSK144_NOALLOC_MAX_BLOCKS
 IQ_U8, IQ_S8, IQ_S16 = 1, 2, 3
@@ -132,6 +132,8 @@ def lib():
         L.msk144_run_device.argtypes = [vp, vp, sz, C.c_int, vp, C.POINTER(C.c_int64)]
         L.msk144_frontend_host.argtypes = [vp, vp, sz, vp, vp, C.POINTER(C.c_int64)]
         L.msk144_frontend_device_noalloc.argtypes = [vp, sz, C.c_int, vp, vp, vp, C.POINTER(C.c_int64)]
+        L.msk144_decode_chunk_host.argtypes = [vp, vp, sz, C.c_int64, vp, sz, C.POINTER(sz), vp, sz, C.POINTER(C.c_int64)]
+        L.msk144_replay_channel.argtypes = [C.c_int32, C.c_int32, C.c_int64, C.c_int64, vp, vp, sz, C.POINTER(Line), sz, C.POINTER(sz)]
         L.msk144_scan_host.argtypes = [vp, vp, C.c_int64, vp, vp, vp, sz, C.POINTER(sz)]
         L.msk144_ldpc_decode_host.argtypes = [vp, vp, sz, vp, vp, vp, vp]
         L.msk144_ldpc_decode_device.argtypes = [vp, vp, sz, vp, vp]
@@ -255,6 +257,23 @@ class Decoder:
         spc = samples.nbytes // 2 // nchan
         fn = lib().msk144_decode_host_interleaved if interleaved else lib().msk144_decode_host
         return self._decode(fn, samples.ctypes.data, spc, nchan, (), line_cap, result_cap)
+
+    def decode_chunk_host(self, samples: np.ndarray, block_base: int = 0, result_cap: int = 1 << 16):
+        """GPU stages of a contiguous piece of ONE channel that starts at block `block_base` (msk144_decode_chunk_host):
+        returns (results, powers[nblocks, 8]); no SNR, no text -- `replay_channel` does both over the pieces in order."""
+        samples = np.ascontiguousarray(samples)
+        ns = samples.nbytes // 2
+        nb = (ns - BLOCK_SAMPLES) // HOP_SAMPLES + 1 if ns >= BLOCK_SAMPLES else 0
+        results = np.zeros(max(result_cap, 1), RESULT_DTYPE)
+        powers = np.zeros((nb, 8), np.float32)
+        nr, got = C.c_size_t(0), C.c_int64(0)
+        rc = lib().msk144_decode_chunk_host(self._h, samples.ctypes.data, ns, block_base, results.ctypes.data, results.size,
+                                            C.byref(nr), powers.ctypes.data, nb, C.byref(got))
+        if rc == -5:
+            results = np.zeros(nr.value, RESULT_DTYPE)
+            rc = lib().msk144_last_output(self._h, None, 0, None, results.ctypes.data, results.size, C.byref(nr))
+        _check(rc)
+        return results[:nr.value].copy(), powers
 
     def deinterleave_device(self, d_in: int, d_out: int, samples_per_channel: int, nchan: int, stream: int = 0):
         _check(lib().msk144_deinterleave_device(self._h, d_in, d_out, samples_per_channel, nchan, C.c_void_p(stream)))
@@ -544,6 +563,38 @@ def frontend_device_noalloc(d_samples: int, nsamples: int, read_mode: int, d_blo
     n = C.c_int64(0)
     _check(lib().msk144_frontend_device_noalloc(d_samples, nsamples, read_mode, d_blocks, d_powers, stream, C.byref(n)))
     return n.value
+
+
+def chunk_ranges(nblocks: int, parts: int) -> List[Tuple[int, int]]:
+    """Contiguous, balanced block ranges [b0, b1) of one channel for `parts` decoders (the first nblocks % parts get one
+    more); the piece of blocks [b0, b1) is samples [2592 b0, 2592 (b1 - 1) + 5184)."""
+    base, extra = divmod(nblocks, parts)
+    out, b = [], 0
+    for j in range(parts):
+        e = b + base + (1 if j < extra else 0)
+        out.append((b, e))
+        b = e
+    return out
+
+
+def replay_channel(powers: np.ndarray, results: np.ndarray, channel: int = 0, first_block: int = 0,
+                   compat_cache: bool = False) -> List[dict]:
+    """The ordered host pass over the output of `Decoder.decode_chunk_host` pieces (msk144_replay_channel, host only):
+    powers [nblocks, 8] and results concatenated in block order -> the decode lines of the undivided channel."""
+    powers = np.ascontiguousarray(powers, np.float32).reshape(-1, 8)
+    results = np.ascontiguousarray(results, RESULT_DTYPE)
+    flags = FLAG_COMPAT_DECODE_CACHE if compat_cache else 0
+    cap = 4096
+    while True:
+        lines = (Line * cap)()
+        n = C.c_size_t(0)
+        rc = lib().msk144_replay_channel(flags, channel, first_block, powers.shape[0], powers.ctypes.data,
+                                         results.ctypes.data if results.size else None, results.size, lines, cap, C.byref(n))
+        if rc == -5 and n.value > cap:
+            cap = n.value
+            continue
+        _check(rc)
+        return [_line_dict(lines[i]) for i in range(n.value)]
 
 
 def decode_message(bits77: np.ndarray) -> Optional[str]:

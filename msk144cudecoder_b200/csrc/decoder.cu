@@ -186,6 +186,24 @@ struct ChanState {
     }
 };
 
+// ResultFilter output of one block (postproc.cpp) as C ABI lines
+void append_block_lines(const std::vector<mskhost::Line>& bl, int64_t block_index, int channel, std::vector<msk144_line>* lines) {
+    for (const auto& l : bl) {
+        msk144_line o;
+        std::memset(&o, 0, sizeof(o));
+        o.block_index = block_index;
+        o.channel = channel;
+        o.snr = l.snr;
+        o.f0 = l.f0;
+        o.num_avg = l.num_avg;
+        o.nbadsync = l.nbadsync;
+        o.pattern_idx = l.pattern_idx;
+        std::memcpy(o.payload, l.payload, 80);
+        std::snprintf(o.text, sizeof(o.text), "%s", l.message.c_str());
+        lines->push_back(o);
+    }
+}
+
 }  // namespace
 
 struct msk144_decoder {
@@ -233,6 +251,7 @@ struct msk144_decoder {
     bool sleep_wait = false;  // set per decode: the flag is on and the call is a live hop (a few blocks)
     int host_wait(cudaStream_t s);
     int upload_pieces(const void* h_src, size_t bytes);
+    std::vector<float>* powers_sink = nullptr;  // msk144_decode_chunk_host: decode_common also hands the sub-block powers out
     int wait_for_input(size_t end_byte, cudaStream_t st);
     float2* d_twiddle = nullptr;
     float* d_hfilt = nullptr;
@@ -627,23 +646,10 @@ int msk144_decoder::decode_common(const void* d_in, size_t spc, int nchan, cudaS
                 ri++;
             }
             if (lines && !present.empty()) {
-                const auto bl = mskhost::block_lines(present, compat, snr->snr_i(), cs->hash);
-                for (const auto& l : bl) {
-                    msk144_line o;
-                    std::memset(&o, 0, sizeof(o));
-                    o.block_index = block_index_base + k;
-                    o.channel = ch;
-                    o.snr = l.snr;
-                    o.f0 = l.f0;
-                    o.num_avg = l.num_avg;
-                    o.nbadsync = l.nbadsync;
-                    o.pattern_idx = l.pattern_idx;
-                    std::memcpy(o.payload, l.payload, 80);
-                    std::snprintf(o.text, sizeof(o.text), "%s", l.message.c_str());
-                    lines->push_back(o);
-                }
+                append_block_lines(mskhost::block_lines(present, compat, snr->snr_i(), cs->hash), block_index_base + k, ch, lines);
             }
         }
+        if (powers_sink) powers_sink->insert(powers_sink->end(), powers.begin(), powers.begin() + static_cast<size_t>(nb) * 8);
         raw.clear();
         powers.clear();
     };
@@ -879,6 +885,72 @@ int msk144_decode_host(msk144_decoder* dec, const void* samples, size_t spc, int
     dec->up_pieces = 0;
     if (dec->up_stream) cudaStreamSynchronize(dec->up_stream);
     if (!upload_err.empty()) return fail(rc, upload_err);
+    return rc;
+}
+
+// ---- one channel split in time (SURVEY.md section 8e "Partitioning"): GPU stages per piece, one ordered host pass ----
+int msk144_decode_chunk_host(msk144_decoder* dec, const void* samples, size_t nsamples, int64_t block_base,
+                             msk144_result* results, size_t result_cap, size_t* nresults, float* powers8,
+                             size_t power_cap_blocks, int64_t* nblocks_out) {
+    if (!dec || !samples) return fail(MSK144_EINVAL, "bad argument");
+    const int64_t nb = nsamples >= static_cast<size_t>(N) ? static_cast<int64_t>((nsamples - N) / (N / 2)) + 1 : 0;
+    if (nblocks_out) *nblocks_out = nb;
+    if (nresults) *nresults = 0;
+    if (powers8 && power_cap_blocks < static_cast<size_t>(nb)) return fail(MSK144_EINVAL, "powers8 holds fewer blocks than the piece has");
+    CK(cudaSetDevice(dec->cfg.device));
+    const size_t bytes = nsamples * 2;
+    if (int rc = dec->ensure_raw(bytes)) return rc;
+    std::vector<msk144_result> rv;
+    std::vector<float> pw;
+    int rc = dec->upload_pieces(samples, bytes);
+    std::string err;
+    if (rc == MSK144_OK) {
+        dec->powers_sink = &pw;
+        // lines == nullptr: no SNR index is used and no text is decoded here; the caller replays both in stream order
+        rc = dec->decode_common(dec->d_raw, nsamples, 1, dec->stream, block_base, nullptr, nullptr, &rv);
+        dec->powers_sink = nullptr;
+    }
+    if (rc != MSK144_OK) err = g_err;
+    dec->up_pieces = 0;
+    if (dec->up_stream) cudaStreamSynchronize(dec->up_stream);
+    if (rc != MSK144_OK) return fail(rc, err);
+    if (powers8) std::memcpy(powers8, pw.data(), pw.size() * sizeof(float));
+    copy_out({}, rv, nullptr, 0, nullptr, results, result_cap, nresults, &rc);
+    dec->last_lines.clear();
+    dec->last_results = std::move(rv);  // after MSK144_EOVERFLOW: msk144_last_output with an array of *nresults
+    return rc;
+}
+
+int msk144_replay_channel(int32_t flags, int32_t channel, int64_t first_block, int64_t nblocks, const float* powers8,
+                          const msk144_result* results, size_t nresults, msk144_line* lines, size_t line_cap,
+                          size_t* nlines) {
+    if (nblocks < 0 || (nblocks && !powers8) || (nresults && !results)) return fail(MSK144_EINVAL, "bad argument");
+    const bool compat = (flags & MSK144_FLAG_COMPAT_DECODE_CACHE) != 0;
+    ChanState cs;  // a fresh SNR recurrence and fresh call-sign tables, as at the start of a channel
+    std::vector<msk144_line> lv;
+    size_t ri = 0;
+    for (int64_t k = 0; k < nblocks; k++) {
+        const int64_t gb = first_block + k;
+        cs.snr.process_powers(powers8 + static_cast<size_t>(k) * 8);
+        if (ri < nresults && results[ri].block_index < gb) return fail(MSK144_EINVAL, "results are not in block order");
+        std::vector<mskhost::Present> present;
+        while (ri < nresults && results[ri].block_index == gb) {
+            const msk144_result& r = results[ri++];
+            if (!present.empty() && r.item_index <= present.back().item) return fail(MSK144_EINVAL, "results of a block are not in item order");
+            mskhost::Present p;
+            p.item = r.item_index;
+            p.f0 = r.f0;
+            p.pattern_idx = static_cast<int>(r.pattern_idx);
+            p.num_avg = r.num_avg;
+            p.nbadsync = r.nbadsync;
+            std::memcpy(p.message, r.message, sizeof(p.message));
+            present.push_back(p);
+        }
+        if (!present.empty()) append_block_lines(mskhost::block_lines(present, compat, cs.snr.snr_i(), cs.hash), gb, channel, &lv);
+    }
+    if (ri != nresults) return fail(MSK144_EINVAL, "results beyond the last block");
+    int rc = MSK144_OK;
+    copy_out(lv, {}, lines, line_cap, nlines, nullptr, 0, nullptr, &rc);
     return rc;
 }
 

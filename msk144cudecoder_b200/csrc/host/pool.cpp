@@ -33,6 +33,7 @@ void split(int nchan, int n, std::vector<int>* first, std::vector<int>* count) {
 }  // namespace
 
 struct msk144_pool {
+    msk144_config cfg{};
     std::vector<msk144_decoder*> dec;
     std::vector<int> device;
     std::vector<msk144_line> last_lines;      // merged output of the most recent msk144_pool_decode_host
@@ -56,6 +57,7 @@ int msk144_pool_create(const msk144_config* cfg, const int32_t* devices, int32_t
     if (!cfg || !out || !devices || ndevices < 1) return pfail(MSK144_EINVAL, "bad argument");
     *out = nullptr;
     msk144_pool* p = new msk144_pool();
+    p->cfg = *cfg;
     for (int i = 0; i < ndevices; i++) {
         msk144_config c = *cfg;
         c.device = devices[i];
@@ -86,11 +88,96 @@ msk144_decoder* msk144_pool_member(msk144_pool* p, int32_t i) {
     return (p && i >= 0 && i < static_cast<int>(p->dec.size())) ? p->dec[i] : nullptr;
 }
 
+// Fewer channels than members: channel c gets members [mfirst[c], mfirst[c] + mcount[c]) and its blocks are cut into
+// that many contiguous ranges (SURVEY.md section 8e "Partitioning").  A member runs the GPU stages of its range from
+// samples [2592 b0, 2592 (b1 - 1) + 5184) of the channel; what crosses blocks (SNR recurrence, hash tables) is replayed
+// here once per channel, in block order, over the members' powers and LDPC successes.
+static int pool_decode_time_split(msk144_pool* p, const void* samples, size_t spc, int nchan) {
+    const int n = static_cast<int>(p->dec.size());
+    const int64_t bpc = spc >= MSK144_BLOCK_SAMPLES ? static_cast<int64_t>((spc - MSK144_BLOCK_SAMPLES) / MSK144_HOP_SAMPLES) + 1 : 0;
+    std::vector<int> mfirst, mcount;
+    split(n, nchan, &mfirst, &mcount);
+    struct Part {
+        int channel = -1;
+        int64_t b0 = 0, b1 = 0;
+        std::vector<msk144_result> results;
+        std::vector<float> powers;
+        int rc = MSK144_OK;
+        std::string err;
+    };
+    std::vector<Part> part(n);
+    for (int c = 0; c < nchan; c++) {
+        const int64_t base = bpc / mcount[c], extra = bpc % mcount[c];
+        int64_t b = 0;
+        for (int j = 0; j < mcount[c]; j++) {
+            Part& pt = part[mfirst[c] + j];
+            pt.channel = c, pt.b0 = b, pt.b1 = b + base + (j < extra ? 1 : 0);
+            b = pt.b1;
+        }
+    }
+    auto work = [&](int i) {
+        Part& pt = part[i];
+        const int64_t nb = pt.b1 - pt.b0;
+        if (pt.channel < 0 || nb <= 0) return;
+        const char* src = static_cast<const char*>(samples) +
+                          (static_cast<size_t>(pt.channel) * spc + static_cast<size_t>(pt.b0) * MSK144_HOP_SAMPLES) * 2;
+        const size_t ns = static_cast<size_t>(nb - 1) * MSK144_HOP_SAMPLES + MSK144_BLOCK_SAMPLES;
+        size_t rcap = 1u << 16, nr = 0;
+        int64_t got = 0;
+        pt.results.resize(rcap);
+        pt.powers.resize(static_cast<size_t>(nb) * 8);
+        pt.rc = msk144_decode_chunk_host(p->dec[i], src, ns, pt.b0, pt.results.data(), rcap, &nr, pt.powers.data(),
+                                         static_cast<size_t>(nb), &got);
+        if (pt.rc == MSK144_EOVERFLOW) {
+            rcap = nr;
+            pt.results.resize(rcap);
+            pt.rc = msk144_last_output(p->dec[i], nullptr, 0, nullptr, pt.results.data(), rcap, &nr);
+        }
+        if (pt.rc != MSK144_OK) pt.err = msk144_last_error();
+        pt.results.resize(std::min(nr, rcap));
+    };
+    std::vector<std::thread> th;
+    for (int i = 1; i < n; i++) th.emplace_back(work, i);
+    work(0);
+    for (auto& t : th) t.join();
+    for (int i = 0; i < n; i++)
+        if (part[i].rc != MSK144_OK) return pfail(part[i].rc, "device " + std::to_string(p->device[i]) + ": " + part[i].err);
+    p->last_lines.clear(), p->last_results.clear();
+    std::vector<float> powers;
+    std::vector<msk144_line> lv;
+    for (int c = 0; c < nchan; c++) {
+        const size_t r0 = p->last_results.size();
+        powers.clear();
+        for (int j = 0; j < mcount[c]; j++) {
+            Part& pt = part[mfirst[c] + j];
+            powers.insert(powers.end(), pt.powers.begin(), pt.powers.end());
+            p->last_results.insert(p->last_results.end(), pt.results.begin(), pt.results.end());
+        }
+        size_t nl = 0;
+        lv.resize(std::max<size_t>(lv.size(), 4096));
+        int rc = msk144_replay_channel(p->cfg.flags, c, 0, bpc, powers.data(), p->last_results.data() + r0,
+                                       p->last_results.size() - r0, lv.data(), lv.size(), &nl);
+        if (rc == MSK144_EOVERFLOW) {
+            lv.resize(nl);
+            rc = msk144_replay_channel(p->cfg.flags, c, 0, bpc, powers.data(), p->last_results.data() + r0,
+                                       p->last_results.size() - r0, lv.data(), lv.size(), &nl);
+        }
+        if (rc != MSK144_OK) return pfail(rc, std::string("replay: ") + msk144_last_error());
+        p->last_lines.insert(p->last_lines.end(), lv.begin(), lv.begin() + nl);
+        for (size_t k = r0; k < p->last_results.size(); k++) p->last_results[k].channel = c;
+    }
+    return MSK144_OK;
+}
+
 int msk144_pool_decode_host(msk144_pool* p, const void* samples, size_t spc, int nchan, msk144_line* lines,
                             size_t line_cap, size_t* nlines, msk144_result* results, size_t result_cap,
                             size_t* nresults) {
     if (!p || !samples || nchan < 1) return pfail(MSK144_EINVAL, "bad argument");
     const int n = static_cast<int>(p->dec.size());
+    if (nchan < n) {
+        if (int rc = pool_decode_time_split(p, samples, spc, nchan)) return rc;
+        return msk144_pool_last_output(p, lines, line_cap, nlines, results, result_cap, nresults);
+    }
     std::vector<int> first, count;
     split(nchan, n, &first, &count);
     struct Part {

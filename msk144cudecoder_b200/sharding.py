@@ -6,9 +6,13 @@ used only to gather the few bytes of text at the end, the host-side gather the n
 any backend (nccl on the GPUs, gloo in CPU tests).  Inside ONE process the same partition is done natively by
 msk144_pool_* (csrc/host/pool.cpp, `msk144cudecoder_b200.Pool`).
 
-One stream is NOT split in time across ranks: besides the half-block input overlap, a stream carries the SNR
-noise-floor recurrence (snr_tracker.cu:39-50) and the call-sign hash tables of its text decoder from block to
-block, so time shards would print other `snr=` values and `<...>` fields than the sequential reference.
+One stream CAN also be split in time across ranks (`decode_time_sharded`): on the device a block needs only its
+own 5184 samples (consecutive blocks overlap by half, main.cu:284-288).  What a stream carries from block to block
+lives on the host -- the SNR noise-floor recurrence (snr_tracker.cu:39-50) and the call-sign hash tables of the text
+decoder -- so the ranks run only the GPU stages of their block range and return (sub-block powers, LDPC successes);
+rank 0 replays SNR and text once, in block order (`replay_channel`), and prints the sequential decoder's lines,
+`snr=` values and `<...>` fields included.  Natively in one process: msk144_pool_decode_host with fewer channels
+than members.
 """
 from __future__ import annotations
 
@@ -56,3 +60,32 @@ def decode_sharded_batch(decode_channels: Callable[[List[int]], Sequence[dict]],
     chans = channels_of_rank(nchan, rank, world)
     mine = [dict(l, channel=chans[l["channel"]]) for l in decode_channels(chans)] if chans else []
     return gather_lines(mine, rank, world) if gather else _order(mine)
+
+
+def gather_time_pieces(powers, results, rank: int, world: int):
+    """Rank 0 gets the pieces of every rank concatenated in rank (= block) order; other ranks get None."""
+    import numpy as np
+    if world == 1:
+        return powers, results
+    import torch.distributed as dist
+    bucket = [None] * world if rank == 0 else None
+    dist.gather_object((powers, results), bucket, dst=0)
+    if rank != 0:
+        return None
+    return np.concatenate([b[0] for b in bucket]), np.concatenate([b[1] for b in bucket])
+
+
+def decode_time_sharded(decode_chunk: Callable[[int, int], tuple], replay: Callable, nblocks: int, rank: int, world: int):
+    """ONE channel of `nblocks` blocks over `world` ranks: `decode_chunk(b0, b1)` runs the GPU stages of blocks [b0, b1)
+    (e.g. `lambda b0, b1: dec.decode_chunk_host(x[2592 * b0: 2592 * (b1 - 1) + 5184], b0)`) and returns (results,
+    powers); `replay(powers, results)` is the ordered host pass (`msk144cudecoder_b200.replay_channel`).  Rank 0
+    returns the decode lines of the whole channel, the others an empty list."""
+    import numpy as np
+    from . import RESULT_DTYPE, chunk_ranges
+    b0, b1 = chunk_ranges(nblocks, world)[rank]
+    if b1 > b0:
+        results, powers = decode_chunk(b0, b1)
+    else:
+        results, powers = np.zeros(0, RESULT_DTYPE), np.zeros((0, 8), np.float32)
+    got = gather_time_pieces(powers, results, rank, world)
+    return list(replay(*got)) if got is not None else []

@@ -197,3 +197,56 @@ def test_small_output_arrays_do_not_cost_a_second_decode(gpu, synth):
     with gpu.Pool([0, 0], compat_cache=True, **KW) as p:
         pooled, pres = p.decode_host(x, nchan=NCHAN, line_cap=1, result_cap=1)
     assert strip(pooled) == strip(big) and pres.tobytes() == bres.tobytes()
+
+
+def hashed_call_stream(synth, seconds=24.0):
+    """One channel whose text depends on stream order: a type-4 message early teaches the hash of PJ4/K1ABC, messages
+    that carry only that hash follow late (they print <PJ4/K1ABC> after it, <...> before), a strong ping moves the SNR
+    noise floor; the rest is cfg2-like noise with weak pings."""
+    n = int(seconds * 12000)
+    P = synth.Ping
+    pings = [P(start=6000, nframes=7, f0=1480.0, snr_db=8.0, text="CQ PJ4/K1ABC"),
+             P(start=40000, nframes=20, f0=1530.0, snr_db=14.0, text="K1ABC W9XYZ EN37"),
+             P(start=n // 2 + 9000, nframes=7, f0=1500.0, snr_db=7.0, text="<PJ4/K1ABC> W9XYZ RR73"),
+             P(start=n - 30000, nframes=7, f0=1460.0, snr_db=6.0, text="W9XYZ <PJ4/K1ABC> RRR"),
+             P(start=n - 14000, nframes=5, f0=1520.0, snr_db=3.0, text="CQ K1ABC FN42")]
+    return synth.audio_stream(pings, n, seed=31)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("parts", [2, 3, 7])
+def test_time_chunks_replayed_in_order_equal_the_undivided_decode(gpu, synth, parts):
+    """SURVEY 8e "Partitioning": GPU stages per time piece, ONE ordered host pass.  Lines byte-identical to the
+    undivided decode: snr (a recurrence over all earlier blocks) and hashed call signs (learnt in an earlier piece)
+    included; LDPC successes identical too."""
+    x = hashed_call_stream(synth)
+    nb = (x.size - 5184) // 2592 + 1
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        whole, whole_res = d.decode_host(x)
+        pieces = [d.decode_chunk_host(x[2592 * b0: 2592 * (b1 - 1) + 5184], b0) for b0, b1 in gpu.chunk_ranges(nb, parts)]
+    texts = [l["text"] for l in whole]
+    assert "CQ PJ4/K1ABC" in texts and "<PJ4/K1ABC> W9XYZ RR73" in texts and "W9XYZ <PJ4/K1ABC> RRR" in texts
+    assert len({l["snr"] for l in whole}) > 2
+    res = np.concatenate([p[0] for p in pieces])
+    powers = np.concatenate([p[1] for p in pieces])
+    assert powers.shape == (nb, 8) and res.tobytes() == whole_res.tobytes()
+    assert gpu.replay_channel(powers, res, compat_cache=True) == whole
+    # the second half alone does not know the call sign: order matters, and the replay is what supplies it
+    late = gpu.replay_channel(pieces[-1][1], pieces[-1][0], first_block=gpu.chunk_ranges(nb, parts)[-1][0], compat_cache=True)
+    assert any("<...>" in l["text"] for l in late)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("members,nchan", [(2, 1), (5, 1), (5, 2)])
+def test_pool_splits_channels_in_time_when_members_outnumber_them(gpu, synth, members, nchan):
+    x = hashed_call_stream(synth)
+    xs = np.concatenate([x, x[::-1].copy()][:nchan])
+    with gpu.Decoder(compat_cache=True, **KW) as d:
+        whole, whole_res = d.decode_host(xs, nchan=nchan)
+    with gpu.Pool([0] * members, compat_cache=True, **KW) as p:
+        lines, res = p.decode_host(xs, nchan, result_cap=1 << 16)
+        busy = [gpu.StageTimes() for _ in range(members)]
+        for i, t in enumerate(busy):
+            gpu.lib().msk144_get_stage_times(gpu.lib().msk144_pool_member(p._h, i), __import__("ctypes").byref(t))
+    assert len(whole) > 3 and lines == whole and res.tobytes() == whole_res.tobytes()
+    assert all(t.blocks > 0 for t in busy), [t.blocks for t in busy]     # every member took a share of the blocks
