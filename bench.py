@@ -293,6 +293,7 @@ def main():
     ap.add_argument("--no-full-stream", action="store_true", help="skip the one whole-stream pass of the CLI legs")
     ap.add_argument("--no-cli", action="store_true", help="skip the CLI / reference-check legs of our arm")
     ap.add_argument("--cfg5-channels", type=int, default=1024, help="channels of the multi-channel leg (0 = skip)")
+    ap.add_argument("--no-one-stream", action="store_true", help="skip the one-stream-over-all-ranks leg")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -422,6 +423,47 @@ def main():
                     "timing": "wall clock between barriers, max over ranks (includes host text decode and the gather); 1 warm-up + 1 timed pass"}
         del x5p
 
+    # ---- ONE stream over all ranks: rank 0's 15-min stream cut into contiguous block ranges (SURVEY.md 8e
+    # "Partitioning"); every rank runs the GPU stages of its range from pinned host samples, rank 0 gathers (powers, LDPC
+    # successes) and replays SNR + text once in block order; all of it inside the timed pass ----
+    one_stream = None
+    if not args.no_one_stream:
+        x1 = x_dev.clone()
+        if world > 1:
+            dist.broadcast(x1.view(torch.uint8), src=0)      # (NCCL has no int16) outside the timed region: every rank holds the capture, as it would a file
+        x1p = x1.cpu().pin_memory()
+        del x1
+        x1n = x1p.numpy()
+
+        def one_pass():
+            t_a = time.perf_counter()
+            out = sharding.decode_time_sharded(
+                lambda b0, b1: dec.decode_chunk_host(x1n[2592 * b0: 2592 * (b1 - 1) + 5184], b0, result_cap=1 << 18),
+                lambda pw, rs: m.replay_channel(pw, rs, compat_cache=True), nblocks, rank, world)
+            return out, time.perf_counter() - t_a
+
+        one_pass()
+        barrier()
+        n1 = max(1, min(args.steps, 3))
+        t0 = time.perf_counter()
+        for _ in range(n1):
+            got1, _ = one_pass()
+            barrier()
+        t1 = torch.tensor([(time.perf_counter() - t0) / n1], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t1, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            b0r, b1r = m.chunk_ranges(nblocks, world)[0]
+            one_stream = {"workload": "the single cfg2 stream of rank 0, blocks cut into contiguous ranges over the ranks "
+                                      "(msk144cudecoder_b200.sharding.decode_time_sharded: msk144_decode_chunk_host per rank, "
+                                      "gather_object of (powers, LDPC successes) to rank 0, msk144_replay_channel there)",
+                          "ranks": world, "blocks": nblocks, "blocks_rank0": b1r - b0r, "passes": n1, "pass_s": float(t1.item()),
+                          "audio_s_per_s": audio_s / float(t1.item()), "lines": len(got1),
+                          "identical_to_undivided_decode": got1 == lines,
+                          "timing": "wall clock between barriers, max over ranks, mean of the passes; pinned host samples in, "
+                                    "decode lines out on rank 0"}
+        del x1p, x1n
+
     if rank == 0:
         hbm_peak, sm_mhz, peak_src = peaks()
         # dominant kernel by measured device time over the timed region
@@ -492,10 +534,13 @@ def main():
                         "messages_sent": len(sent_texts), "false_texts": len(found_texts - sent_texts)},
                 "gpu_launches": int(st["groups"] * 3),
                 "ldpc_codewords_per_s": ncw / dur["ldpc_kernel"] if dur["ldpc_kernel"] > 0 else None,
-                "ldpc_codewords_per_step": int(ncw),
-                "roofline": roofline}
+                "ldpc_codewords_per_step": int(ncw)}
+        # the sharded legs before the (long) roofline object, so that a truncated tail of the line still carries them
+        if one_stream is not None:
+            line["one_stream"] = one_stream
         if cfg5 is not None:
             line["cfg5"] = cfg5
+        line["roofline"] = roofline
         if world == 1 and not args.no_cli:
             # ---- the drop-in executable on the same bytes, and its output against the reference's ----------
             try:
