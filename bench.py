@@ -435,11 +435,23 @@ def main():
         del x1
         x1n = x1p.numpy()
 
+        phase = {"decode_s": 0.0, "replay_s": 0.0}
+
+        def timed_chunk(b0, b1):
+            t_a = time.perf_counter()
+            out = dec.decode_chunk_host(x1n[2592 * b0: 2592 * (b1 - 1) + 5184], b0, result_cap=1 << 17)
+            phase["decode_s"] = time.perf_counter() - t_a
+            return out
+
+        def timed_replay(pw, rs):
+            t_a = time.perf_counter()
+            out = m.replay_channel(pw, rs, compat_cache=True)
+            phase["replay_s"] = time.perf_counter() - t_a
+            return out
+
         def one_pass():
             t_a = time.perf_counter()
-            out = sharding.decode_time_sharded(
-                lambda b0, b1: dec.decode_chunk_host(x1n[2592 * b0: 2592 * (b1 - 1) + 5184], b0, result_cap=1 << 18),
-                lambda pw, rs: m.replay_channel(pw, rs, compat_cache=True), nblocks, rank, world)
+            out = sharding.decode_time_sharded(timed_chunk, timed_replay, nblocks, rank, world)
             return out, time.perf_counter() - t_a
 
         one_pass()
@@ -460,6 +472,8 @@ def main():
                           "ranks": world, "blocks": nblocks, "blocks_rank0": b1r - b0r, "passes": n1, "pass_s": float(t1.item()),
                           "audio_s_per_s": audio_s / float(t1.item()), "lines": len(got1),
                           "identical_to_undivided_decode": got1 == lines,
+                          "rank0_last_pass": {"decode_chunk_s": phase["decode_s"], "replay_s": phase["replay_s"],
+                                              "gather_and_rest_s": max(0.0, float(t1.item()) - phase["decode_s"] - phase["replay_s"])},
                           "timing": "wall clock between barriers, max over ranks, mean of the passes; pinned host samples in, "
                                     "decode lines out on rank 0"}
         del x1p, x1n

@@ -403,3 +403,35 @@ def test_wsjtx_bp_stream_matches_oracle(gpu, orc, synth):
     with gpu.Decoder(compat_cache=True, wsjtx_bp=True, **kw) as d:
         lines, _ = d.decode_host(x)
     assert len(ref) > 0 and lines_key(lines) == lines_key(ref)
+
+
+def test_repeated_runs_are_bit_identical(gpu, synth):
+    """Stand-in for racecheck (compute-sanitizer is closed on this pool): a data race in the shared-memory pipelines of
+    scan_kernel / ldpc_kernel, or in the lock-free queue slots, would make outputs differ between runs of the same
+    input.  Deep-scan settings (depth 8, step 1.5, thr 3), repeated in one decoder and across fresh decoders: every
+    LDPC success, every decode line, every candidate record and every soft bit must be the same bits each time (queue
+    slots are handed out by atomicAdd, so LLR rows are compared by the item they belong to)."""
+    x, _ = synth.cfg2_deep_audio(seconds=6.0, seed=144, npings=6)
+    kw = dict(compat_cache=True, width=60, step=1.5, depth=8, thr=3)
+
+    def stage_view(d):
+        blocks, powers = d.frontend(x)
+        cands, llr, item = d.scan(blocks[:6])
+        order = np.argsort(item, kind="stable")
+        return (blocks.tobytes(), powers.tobytes(), cands["pos"].tobytes(), cands["xb"].tobytes(), cands["nbadsync"].tobytes(),
+                item[order].tobytes(), llr[order].tobytes())
+
+    runs, stages = [], []
+    with gpu.Decoder(**kw) as d:
+        for _ in range(4):
+            lines, res = d.decode_host(x, result_cap=1 << 16)
+            runs.append((lines, res.tobytes()))
+        stages += [stage_view(d), stage_view(d)]
+    for _ in range(2):
+        with gpu.Decoder(**kw) as d:
+            lines, res = d.decode_host(x, result_cap=1 << 16)
+            runs.append((lines, res.tobytes()))
+            stages.append(stage_view(d))
+    assert len(runs[0][1]) > 0 and len(runs[0][0]) > 0
+    assert all(r == runs[0] for r in runs[1:])
+    assert all(s == stages[0] for s in stages[1:])
