@@ -601,6 +601,25 @@ def main():
                                               f"C++ oracle port on {cores} threads, {dt:.1f} s; WSJT-X Fortran decoder "
                                               "unavailable on this box (empty submodule, no gfortran)",
                                     "lines_identical_to_gpu": ours == theirs}
+            # LDPC stage alone on the host cores (SURVEY.md 8d "CPU baseline"): the oracle's restatement of
+            # ldpc_kernel.cuh:100-249 and of WSJT-X's bpdecode128_90 control flow, all threads
+            try:
+                ncw_cpu = 1 << 16
+                rng = np.random.default_rng(7)
+                noise = (5.5 * rng.standard_normal((ncw_cpu, 128))).astype(np.float32)   # like gate-passing candidates: none converges
+                sig, _ = synth.cfg4_llrs(ncw_cpu, 3.0, seed=149)
+                ld = {}
+                for name, fn, arr in (("noise_reference_semantics", orc.ldpc_decode_batch, noise),
+                                      ("noise_wsjtx_semantics", orc.ldpc_decode_wsjtx_batch, noise),
+                                      ("cfg4_ebn0_3db_reference_semantics", orc.ldpc_decode_batch, sig)):
+                    fn(arr[:1024], nthreads=cores)
+                    t0 = time.perf_counter()
+                    fn(arr, nthreads=cores)
+                    ld[name] = ncw_cpu / (time.perf_counter() - t0)
+                line["cpu_baseline"]["ldpc_cw_per_s"] = dict(ld, codewords=ncw_cpu, cores=cores,
+                                                             gpu_same_metric=line["ldpc_codewords_per_s"])
+            except Exception as e:  # noqa: BLE001
+                line["cpu_baseline"]["ldpc_cw_per_s"] = {"error": " ".join(str(e).split())[:200]}
         print(json.dumps(line), flush=True)
     dec.close()
     if world > 1:
