@@ -411,7 +411,10 @@ def test_repeated_runs_are_bit_identical(gpu, synth):
     input.  Deep-scan settings (depth 8, step 1.5, thr 3), repeated in one decoder and across fresh decoders: every
     LDPC success, every decode line, every candidate record and every soft bit must be the same bits each time (queue
     slots are handed out by atomicAdd, so LLR rows are compared by the item they belong to)."""
-    x, _ = synth.cfg2_deep_audio(seconds=6.0, seed=144, npings=6)
+    P = synth.Ping
+    x = synth.audio_stream([P(start=5000, nframes=7, f0=1490.5, snr_db=6.0, text="CQ K1ABC FN42"),
+                            P(start=30000, nframes=10, f0=1512.0, snr_db=1.0, text="K1ABC W9XYZ EN37"),
+                            P(start=52000, nframes=4, f0=1478.0, snr_db=9.0, text="W9XYZ K1ABC R-03")], 6 * 12000, seed=77)
     kw = dict(compat_cache=True, width=60, step=1.5, depth=8, thr=3)
 
     def stage_view(d):
